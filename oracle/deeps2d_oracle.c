@@ -563,10 +563,18 @@ int ohf_step(ohf_node* J, const ohf_cfg* g, unsigned global_iter, int is_src_add
                     } else if (k < 4 + OHF_NCOMP) {
                         cf = CT_Y_CONST; dxf = CT_dYdx_NULL; dyf = CT_dYdy_NULL; dx2f = CT_d2Ydx2_NULL; dy2f = CT_d2Ydy2_NULL;
                     } else if (turb2) {
-                        /* k==i2d_k and k==i2d_eps use the same shift expression (:918-930) */
-                        cf = TCT_k_CONST << (k - 4 - OHF_NCOMP); dxf = TCT_dkdx_NULL << (k - 4 - OHF_NCOMP);
-                        dyf = TCT_dkdy_NULL << (k - 4 - OHF_NCOMP); dx2f = TCT_d2kdx2_NULL << (k - 4 - OHF_NCOMP);
-                        dy2f = TCT_d2kdy2_NULL << (k - 4 - OHF_NCOMP);
+                        /* quirk (:918-930): the eps branch starts from the eps masks AND shifts them by
+                         * (k-7)=1 again, so eps tests 0x04,0x10,0x40,0x100,0x400 -- the last one is the
+                         * k-eps model bit itself, i.e. dy2_flag is always set for the eps equation.     */
+                        if (k == iK) {
+                            cf = TCT_k_CONST << (k - 4 - OHF_NCOMP); dxf = TCT_dkdx_NULL << (k - 4 - OHF_NCOMP);
+                            dyf = TCT_dkdy_NULL << (k - 4 - OHF_NCOMP); dx2f = TCT_d2kdx2_NULL << (k - 4 - OHF_NCOMP);
+                            dy2f = TCT_d2kdy2_NULL << (k - 4 - OHF_NCOMP);
+                        } else if (k == iEps) {
+                            cf = TCT_eps_CONST << (k - 4 - OHF_NCOMP); dxf = (TCT_dkdx_NULL << 1) << (k - 4 - OHF_NCOMP);
+                            dyf = (TCT_dkdy_NULL << 1) << (k - 4 - OHF_NCOMP); dx2f = (TCT_d2kdx2_NULL << 1) << (k - 4 - OHF_NCOMP);
+                            dy2f = (TCT_d2kdy2_NULL << 1) << (k - 4 - OHF_NCOMP);
+                        }
                     }
                     if (k < 4 + OHF_NCOMP) {
                         c_flag = !is_ct(c, cf); dx_flag = !is_ct(c, dxf); dy_flag = !is_ct(c, dyf);

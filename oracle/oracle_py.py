@@ -125,11 +125,16 @@ def make_cfg(cfg: dict):
 
 
 def nodes_from_ref(aos: np.ndarray) -> np.ndarray:
-    """reference AoS record array (nx, ny) -> oracle node array (nx, ny); SN starts as a copy of S."""
+    """reference AoS record array (nx, ny) -> oracle node array (nx, ny).
+
+    SN (the FlowNodeCore2D shadow, "NextNode") starts as zeros: hf2d_start.cpp:318 allocates it with
+    UMatrix2D's zero-filling constructor (utl/umatrix2d.hpp:178) and it then persists across steps, so
+    an equation whose Stage-1 update is skipped but whose Stage-2 commit is not receives 0 (or the
+    last value written)."""
     out = np.zeros(aos.shape, dtype=NODE_DTYPE)
     for name in NODE_DTYPE.names:
         if name == "SN":
-            out["SN"] = aos["S"]
+            continue
         else:
             out[name] = aos[name]
     return out

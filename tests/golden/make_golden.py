@@ -1,0 +1,215 @@
+#!/usr/bin/env python
+"""Generate the golden vectors under tests/golden/ by running the UNMODIFIED reference solver.
+
+Run HERE (build container, /root/reference present):   python tests/golden/make_golden.py
+Needs oracle/_ref/ohf_dump (make -C oracle ref).  For every case below it writes an input deck in
+the reference's own format (authored here, small grids), runs the reference for N steps (one or two
+output cycles), and stores
+    tests/golden/<case>.npz :  state0 / stateN = raw AoS grid images (uint8, zlib-compressed by npz),
+                               cfg = text of every scalar/table the step reads, nx, ny, nsteps, ncycles,
+                               global_time, dt_final, rms_file (the reference's RMS-*.plt text)
+    tests/golden/layout.txt :  FlowNode2D member offsets (offsetof on the reference's header)
+The GPU box has no /root/reference: tests only read the committed .npz files.
+"""
+from __future__ import annotations
+
+import os
+import shutil
+import subprocess
+import sys
+import tempfile
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+DUMP = os.path.join(ROOT, "oracle", "_ref", "ohf_dump")
+
+# ---- property tables (authored; loosely air / H2 / O2 / H2O like, deliberately including a
+# ---- descending-x table and tables whose range does not cover every temperature met) ----------
+TABLES = {
+    "lam_cp": [(800., 0.12), (1200., 0.17), (1600., 0.22), (2400., 0.30), (3400., 0.41)],
+    "mu_cp": [(800., 3.3e-5), (1200., 4.4e-5), (2000., 6.5e-5), (3400., 9.3e-5)],
+    "Cp_cp": [(800., 1540.), (1200., 1620.), (2000., 1770.), (3400., 1930.)],
+    "lam_Fuel": [(200., 0.14), (400., 0.226), (1000., 0.45)],
+    "mu_Fuel": [(20., 2.5e-6), (100., 4.2e-6), (1000., 20.1e-6), (2000., 33.6e-6)],
+    "Cp_Fuel": [(20., 10000.), (400., 14500.), (1500., 16050.)],
+    "lam_OX": [(1700., 0.115), (1000., 0.0755), (600., 0.0465), (300., 0.0262), (230., 0.021)],   # descending
+    "mu_OX": [(1700., 5.9e-5), (1000., 4.2e-5), (600., 2.9e-5), (300., 1.75e-5), (230., 1.4e-5)],  # descending
+    "Cp_OX": [(1700., 1398.), (1000., 1240.), (600., 1130.), (300., 1053.), (230., 1052.)],       # descending
+    "lam_air": [(90., 0.015), (300., 0.0267), (1000., 0.07), (2000., 0.115), (3500., 0.173)],
+    "mu_air": [(100., 7.7e-6), (300., 18.3e-6), (1000., 48.5e-6), (2000., 64.7e-6), (3500., 93.1e-6)],
+    "Cp_air": [(200., 1005.8), (300., 1004.5), (400., 1009.7), (1500., 1210.8), (3500., 1307.4)],
+}
+
+
+def table(name, rows):
+    return [f"<table={name}/{len(rows)}>"] + [f"{x!r} {y!r}" for x, y in rows] + ["<endtable>"]
+
+
+def make_deck(name, *, nx=60, ny=40, dx=1e-3, dy=1e-3, problem=0, flow_type=0, turb=0, turb_ext=0, bff=4,
+              adiabatic=1, alt_rms=1, nmax=2, tf=1000., k0=34., turb_reset=0, turb_start=0, cfl=0.1, beta=0.985,
+              flows=None, bounds=None, contour=None, areas=None, single_bounds=(), monitor_index=5, delta_bl=1e-3,
+              sig_w=1.0, sig_f=1.0, beta_nrbc=0.25):
+    """Return deck text.  `flows`: list of dicts (Flow2D-n.*), `bounds`: list of (cond string, flow2d idx)."""
+    L = [f"<start/{name}>"]
+    d = lambda k, v: L.append(f"<data/{k}={v}>")
+    d("ProjectName", name); d("OutputFile", ".plt"); d("ErrorFile", "-err.plt"); d("GasSwapFile", ".hf2d")
+    d("isAdiabaticWall", adiabatic); d("isOutHeatFluxX", 0); d("isOutHeatFluxY", 0); d("is_p_asterisk_out", 0)
+    d("isIgnoreUnsetNodes", 0); d("ProblemType", problem); d("FlowType", flow_type)
+    d("MaxX", nx); d("MaxY", ny); d("dx", repr(dx)); d("dy", repr(dy))
+    d("isAlternateRMS", alt_rms); d("MonitorIndex", monitor_index); d("ExitMonitorValue", "1.e-30"); d("NumMonitorPoints", 0)
+    d("CFL", repr(cfl))
+    L += table("CFL_Scenario", [(0., cfl * 0.5), (4., cfl), (200000., cfl)])
+    d("beta", repr(beta)); d("beta_NonReflectedBC", repr(beta_nrbc))
+    L += table("beta_Scenario", [(0., beta - 0.03), (6., beta - 0.001), (100000., beta)])
+    d("Nmax", nmax); d("NOutStep", 1); d("NSaveStep", 1); d("isVerboseOutput", 1); d("InitTime", "0.")
+    d("BFF", bff); d("TurbulenceModel", turb); d("isTurbulenceReset", turb_reset); d("ZeroEqFactor", 0)
+    d("SigW", repr(sig_w)); d("SigF", repr(sig_f)); d("delta_bl", repr(delta_bl)); d("TurbStartIter", turb_start); d("TurbExtModel", turb_ext)
+    d("Ts0", "320."); d("K0", repr(k0)); d("gamma", "0."); d("Tf", repr(tf)); d("NumSrc", 0)
+    d("H_cp", "-1.2e7"); d("R_cp", "428.59"); d("H_Fuel", "0.0"); d("R_Fuel", "4157.0")
+    d("H_OX", "50.0e3"); d("R_OX", "290.0"); d("H_air", "0.0"); d("R_air", "287.0")
+    for tn, rows in TABLES.items():
+        L += table(tn, rows)
+    d("NumFlow", 0)
+    d("NumFlow2D", len(flows))
+    for i, f in enumerate(flows, 1):
+        for k, v in f.items():
+            d(f"Flow2D-{i}.{k}", v)
+    d("NumRects", 0); d("NumCircles", 0); d("NumAirfoils", 0)
+    d("NumSingleBounds", len(single_bounds))
+    for i, sb in enumerate(single_bounds, 1):
+        L += table(f"SingleBound{i}.Points", sb["points"])
+        d(f"SingleBound{i}.Cond", sb["cond"]); d(f"SingleBound{i}.Flow2D", sb["flow"])
+        d(f"SingleBound{i}.TurbulenceModel", turb); d(f"SingleBound{i}.isReset", 0); d(f"SingleBound{i}.MaterialID", 0)
+    d("NumContour", 1)
+    L += table("Contour1", contour)
+    d("Contour1.MaterialID", 0)
+    for i, (cond, fl) in enumerate(bounds, 1):
+        d(f"Contour1.Bound{i}.Cond", cond); d(f"Contour1.Bound{i}.Flow2D", fl)
+        d(f"Contour1.Bound{i}.TurbulenceModel", turb); d(f"Contour1.Bound{i}.isReset", 0)
+    d("NumArea", len(areas))
+    for i, a in enumerate(areas, 1):
+        L += [f"<table=Area{i}/1>", f"{a['seed'][0]} {a['seed'][1]}", "<endtable>"]
+        d(f"Area{i}.Type", a["type"]); d(f"Area{i}.MaterialID", a.get("mat", 0))
+        if a["type"] == 1:
+            d(f"Area{i}.Flow2D", a["flow"]); d(f"Area{i}.TurbulenceModel", turb)
+    d("is_Cx_calc", 0); d("is_Cd_calc", 0); d("x_body", "0.0"); d("y_body", "0.0"); d("dx_body", "0.0"); d("dy_body", "0.0")
+    d("Cx_Flow_Index", 1); d("NumXCut", 0)
+    L.append(f"<end/{name}>")
+    return "\n".join(L) + "\n"
+
+
+def air(mach=None, p=101350., T=288.9, comp=3, angle=0.0):
+    if mach is None:
+        return {"CompIndex": comp, "Mode": 0, "p": p, "T": T, "U": 0.0, "V": 0.0}
+    return {"CompIndex": comp, "Mode": 2, "Mach": mach, "Angle": angle, "p": p, "T": T, "U": 0.0, "V": 0.0}
+
+
+def wedge_geometry(nx, ny, dx, dy, ramp_x, ramp_h):
+    X, Y = nx * dx, ny * dy
+    xr = X - 1e-5
+    return [(0.0, Y), (xr, Y), (xr, ramp_h), (ramp_x, 0.0), (0.0, 0.0)]
+
+
+def cases():
+    C = {}
+    nx, ny, dx, dy = 60, 40, 1e-3, 1e-3
+    geo = wedge_geometry(nx, ny, dx, dy, 0.02, 0.011)
+    areas = [{"seed": (3, 3), "type": 1, "flow": 1}, {"seed": (nx - 4, 2), "type": 0, "mat": 1}]
+    # 1. Euler duct with ramp (BASELINE config 1 in miniature): FC inflow, D0X outflow, symmetric floor, slip ramp
+    euler_b = [("NT_FC_2D", 1), ("NT_D0X_2D", 1), ("NT_D0Y_2D, CT_V_CONST_2D", 2), ("NT_D0Y_2D, CT_V_CONST_2D", 2), ("NT_FC_2D", 1)]
+    C["euler_duct"] = dict(deck=dict(problem=0, flows=[air(2.5), air()], bounds=euler_b, contour=geo, areas=areas, bff=4), steps=[1, 10])
+    C["euler_duct_bff5"] = dict(deck=dict(problem=0, flows=[air(2.5), air()], bounds=euler_b, contour=geo, areas=areas, bff=5, alt_rms=0,
+                                          monitor_index=0), steps=[7])
+    # 2. laminar NS with a no-slip ramp, adiabatic
+    ns_b = [("NT_FARFIELD_2D", 1), ("NT_D0X_2D, CT_NONREFLECTED_2D", 1), ("NT_WNS_2D", 2), ("NT_D0Y_2D, CT_V_CONST_2D", 2), ("NT_FARFIELD_2D", 1)]
+    C["ns_laminar"] = dict(deck=dict(problem=1, turb=0, flows=[air(2.5), air()], bounds=ns_b, contour=geo, areas=areas), steps=[1, 8], two_cycle=4)
+    # 3. k-eps (std) with non-adiabatic wall -> CalcHeatOnWallSources
+    ke_b = [("NT_FARFIELD_2D, TCT_k_CONST_2D, TCT_eps_CONST_2D", 1),
+            ("NT_D0X_2D, TCT_dkdx_NULL_2D, TCT_depsdx_NULL_2D,  CT_NONREFLECTED_2D", 1),
+            ("NT_WNS_2D, TCT_eps_Cmk2kXn_WALL_2D", 2),
+            ("NT_D0Y_2D, TCT_dkdy_NULL_2D, TCT_depsdy_NULL_2D, CT_V_CONST_2D", 2),
+            ("NT_FARFIELD_2D, TCT_k_CONST_2D, TCT_eps_CONST_2D", 1)]
+    for tag, tem in (("std", 4), ("chien", 5), ("jl", 6), ("lsy", 7), ("rng", 8)):
+        C[f"ns_keps_{tag}"] = dict(deck=dict(problem=1, turb=4, turb_ext=tem, turb_reset=1, turb_start=1, adiabatic=0,
+                                             flows=[air(2.5), air()], bounds=ke_b, contour=geo, areas=areas),
+                                   steps=[8] if tag != "std" else [1, 8], two_cycle=4 if tag == "std" else None)
+    # 4. Spalart-Allmaras
+    sa_b = [("NT_FARFIELD_2D, TCT_k_CONST_2D", 1), ("NT_D0X_2D, TCT_dkdx_NULL_2D, CT_NONREFLECTED_2D", 1), ("NT_WNS_2D", 2),
+            ("NT_D0Y_2D, TCT_dkdy_NULL_2D, CT_V_CONST_2D", 2), ("NT_FARFIELD_2D, TCT_k_CONST_2D", 1)]
+    C["ns_sa"] = dict(deck=dict(problem=1, turb=3, turb_ext=10, turb_reset=1, turb_start=2, flows=[air(2.5), air()], bounds=sa_b,
+                                contour=geo, areas=areas), steps=[8], two_cycle=4)
+    # 5. zero-equation (van Driest) and Smagorinsky
+    C["ns_prandtl_vd"] = dict(deck=dict(problem=1, turb=2, turb_ext=1, turb_start=0, flows=[air(2.5), air()], bounds=ns_b, contour=geo,
+                                        areas=areas, bff=5), steps=[8])
+    C["ns_klebanoff"] = dict(deck=dict(problem=1, turb=2, turb_ext=3, turb_start=0, flows=[air(2.5), air()], bounds=ns_b, contour=geo,
+                                       areas=areas, delta_bl=4e-3), steps=[6])
+    C["ns_smagorinsky"] = dict(deck=dict(problem=1, turb=5, turb_ext=15, turb_start=0, flows=[air(2.5), air()], bounds=ns_b, contour=geo,
+                                         areas=areas), steps=[8])
+    # 6. axisymmetric, multicomponent, reacting: hot oxidiser co-flow (Flow2D-1), cold fuel jet on the lower part of the
+    #    inflow face (SingleBound, Flow2D-3), ignition temperature below the co-flow temperature so the burn branch fires.
+    ax_geo = [(0.0, ny * dy), (nx * dx - 1e-5, ny * dy), (nx * dx - 1e-5, 0.0), (0.0, 0.0)]
+    ax_b = [("NT_D0Y_2D", 1), ("NT_D0X_2D", 1), ("NT_AX_2D", 1), ("NT_FC_2D", 1)]
+    jet = [{"points": [(0.0, 0.0), (0.0, 0.012)], "cond": "NT_FC_2D", "flow": 3}]
+    ax_flows = [air(1.5, p=101350., T=1400., comp=1), air(comp=1, T=1400.), air(1.2, p=101350., T=400., comp=0)]
+    C["axi_reacting_euler"] = dict(deck=dict(problem=0, flow_type=1, flows=ax_flows, bounds=ax_b, contour=ax_geo,
+                                             areas=[{"seed": (5, 20), "type": 1, "flow": 1}], single_bounds=jet, tf=900., k0=8.0), steps=[10])
+    ax_kb = [("NT_D0Y_2D, TCT_dkdy_NULL_2D, TCT_depsdy_NULL_2D", 1), ("NT_D0X_2D, TCT_dkdx_NULL_2D, TCT_depsdx_NULL_2D", 1),
+             ("NT_AX_2D, TCT_dkdy_NULL_2D, TCT_depsdy_NULL_2D", 1), ("NT_FC_2D, TCT_k_CONST_2D, TCT_eps_CONST_2D", 1)]
+    jet_k = [{"points": [(0.0, 0.0), (0.0, 0.012)], "cond": "NT_FC_2D, TCT_k_CONST_2D, TCT_eps_CONST_2D", "flow": 3}]
+    C["axi_reacting_keps"] = dict(deck=dict(problem=1, flow_type=1, turb=4, turb_ext=4, turb_reset=1, turb_start=1, flows=ax_flows,
+                                            bounds=ax_kb, contour=ax_geo, areas=[{"seed": (5, 20), "type": 1, "flow": 1}],
+                                            single_bounds=jet_k, tf=900., k0=8.0), steps=[8])
+    return C
+
+
+def run_ref(deck_text, name, nstep, exit_time, wd):
+    os.makedirs(wd, exist_ok=True)
+    for f in os.listdir(wd):
+        os.remove(os.path.join(wd, f))
+    with open(os.path.join(wd, name + ".dat"), "w") as f:
+        f.write(deck_text)
+    env = dict(os.environ, OHF_DUMP_DIR=wd, OHF_EXIT_TIME=repr(exit_time), OHF_NSTEP=str(nstep))
+    with open(os.path.join(wd, "log.txt"), "w") as log:
+        subprocess.run([DUMP, name + ".dat"], cwd=wd, env=env, stdout=log, stderr=subprocess.STDOUT, check=True, timeout=600)
+    fin = dict(l.split() for l in open(os.path.join(wd, "final.txt")))
+    return fin
+
+
+def main(only=None):
+    assert os.path.exists(DUMP), "build oracle/_ref first: make -C oracle ref"
+    tmp = tempfile.mkdtemp(prefix="ohf_golden_")
+    first = True
+    for cname, spec in cases().items():
+        if only and cname not in only:
+            continue
+        runs = [(n, 1) for n in spec["steps"]]
+        if spec.get("two_cycle"):
+            runs.append((spec["two_cycle"], 2))
+        for nstep, ncyc in runs:
+            tag = f"{cname}_n{nstep}" + ("x2" if ncyc == 2 else "")
+            deck = make_deck(cname, **spec["deck"])
+            wd = os.path.join(tmp, tag)
+            fin = run_ref(deck, cname, nstep, 1e-300, wd)
+            if ncyc == 2:  # second pass: stop after the 2nd cycle (GlobalTime after 1 cycle < T <= after 2)
+                t1 = float(fin["GlobalTime"])
+                fin = run_ref(deck, cname, nstep, 1.5 * t1, wd)
+            assert int(fin["last_iter"]) == nstep * ncyc, (tag, fin)
+            if not os.path.exists(os.path.join(wd, "state0.hf2d")):
+                raise RuntimeError(open(os.path.join(wd, "log.txt")).read()[-2000:])
+            if first:
+                shutil.copy(os.path.join(wd, "layout.txt"), os.path.join(HERE, "layout.txt"))
+                first = False
+            cfg = open(os.path.join(wd, "cfg.txt")).read()
+            s0 = np.fromfile(os.path.join(wd, "state0.hf2d"), dtype=np.uint8)
+            sN = np.fromfile(os.path.join(wd, cname + ".hf2d"), dtype=np.uint8)
+            rms = open(os.path.join(wd, "RMS-" + cname + ".plt")).read()
+            np.savez_compressed(os.path.join(HERE, tag + ".npz"), state0=s0, stateN=sN, cfg=np.array(cfg), nsteps=nstep, ncycles=ncyc,
+                                global_time=float(fin["GlobalTime"]), dt_final=float(fin["dt"]), rms_file=np.array(rms))
+            print(f"{tag}: {os.path.getsize(os.path.join(HERE, tag + '.npz')) / 1024:.0f} KiB  t={fin['GlobalTime']} dt={fin['dt']}")
+    shutil.rmtree(tmp, ignore_errors=True)
+
+
+if __name__ == "__main__":
+    main(set(sys.argv[1:]) or None)
