@@ -71,6 +71,15 @@ double ohf_table_getval(const ohf_table* t, double x) {
     return t->y[i] + (t->y[i - 1] - t->y[i]) * (x - t->x[i]) / (t->x[i - 1] - t->x[i]);
 }
 
+/* pow(double,int) in the reference's C++98 dialect is std::pow(double,int) = __builtin_powi, which
+ * g++ -O2 expands for a constant exponent along its addition-chain table: x^6 = x^3 * x^3, x^3 = (x*x)*x
+ * (gcc tree-ssa-math-opts powi_as_mults; verified bit-exact against the reference binary).  Only the Klebanoff
+ * mixing length uses it (hyper_flow_node.hpp:632); the SA model calls pow(double,double). */
+static double powi6(double x) {
+    double x3 = (x * x) * x;
+    return x3 * x3;
+}
+
 /* SetTurbulenceModel, deeps2d_core.cpp:4683-4695 */
 static int add_eq(const ohf_node* n) {
     if (is_tt(n, TCT_Prandtl_Model)) return 2;
@@ -162,7 +171,7 @@ static void turb_mod_rans(ohf_node* c, const ohf_cfg* g, int is_mu_t, int is_ini
             if (delta > 0.) l = OMIN(n_0, 0.09 * delta);
             else l = n_0;
         } else if (tem == TEM_Klebanoff) {
-            if (delta > 0.) l = n_0 / sqrt(1 + 5.5 * pow(c->l_min / delta, 6));
+            if (delta > 0.) l = n_0 / sqrt(1 + 5.5 * powi6(c->l_min / delta));
             else l = n_0;
         }
         c->mu_t = c->S[iRho] * l * l * OMAX(fabs(c->dUdy), fabs(c->dVdx));
