@@ -1,0 +1,145 @@
+/* hf2d_gpu.h -- C ABI of the B200-native DEEPS2D time step (libhf2d_gpu.so).
+ *
+ * Drop-in boundary for ONE path of OpenHyperFLOW2D: the inner `do { ... } while(iter < Nstep)` loop of
+ * `DEEPS2D_Run` (libDEEPS2D/deeps2d_core.cpp:735-1642; declaration deeps2d_core.hpp:206-212) -- Stage 1,
+ * Stage 2 (FlowNode2D::FillNode2D / TurbModRANS2D, hyper_flow_node.hpp:374-957), CalcChemicalReactions
+ * (deeps2d_core.cpp:4697-4780), CalcHeatOnWallSources (:2679-2833), the CFL dt reduction (:1318-1326) and the
+ * residual reduction (:1089-1153, :1539-1574).  The reference has no FFI: the seam is that C++ function plus
+ * the file-scope globals it reads (deeps2d_core.hpp:118-151).  A reference-side shim therefore
+ *   1. fills `hf2d_cfg` from those globals                         (replaces: reading them inside the loop),
+ *   2. describes its FlowNode2D record with `hf2d_node_layout`     (offsetof on hyper_flow_node.hpp:138-191),
+ *   3. hf2d_gpu_upload_aos(J->GetMatrixPtr())                      (replaces: SubDomainArray views, hf2d_start.cpp:310-322),
+ *   4. hf2d_gpu_step(Nstep) once per output cycle                  (replaces: deeps2d_core.cpp:735-1642),
+ *   5. hf2d_gpu_download_aos(J->GetMatrixPtr()) before the per-cycle writers run (DataSnapshot :1773, swap-file
+ *      sync :1818-1849, libOutCFD post-processing :1790-1813).
+ * INTEGRATION.md shows that shim.  Plain C types only; every function returns 0 on success or an HF2D_E* code;
+ * hf2d_gpu_last_error() gives a message.  One host thread per handle; one handle per GPU (X-slab).
+ * There is no CPU fallback: without a CUDA device every entry point but the layout/size helpers fails.
+ */
+#ifndef HF2D_GPU_H
+#define HF2D_GPU_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HF2D_NEQ      9    /* FlowNode2D::NumEq = 6 + NUM_COMPONENTS (hyper_flow_node.hpp:255) */
+#define HF2D_NTABLES 14
+
+enum hf2d_status {
+    HF2D_OK = 0,
+    HF2D_EINVAL = 1,       /* bad argument / unsupported configuration                                   */
+    HF2D_ECUDA = 2,        /* CUDA runtime error (no device, out of memory, launch failure)               */
+    HF2D_EUNSTABLE = 3,    /* Tg < 0 met (deeps2d_core.cpp:1246): report.err_i/err_j hold the first node  */
+    HF2D_ESTATE = 4        /* call out of order (e.g. step before upload)                                 */
+};
+
+/* property/scenario table, Table::GetVal semantics (obj_data/obj_data.cpp:1822-1860); n == 0 is the zero table */
+typedef struct hf2d_table { int n; const double* x; const double* y; } hf2d_table;
+
+/* table slots: species s = 0 fuel, 1 oxidiser, 2 combustion products, 3 air (ChemicalReactionsModelData2D,
+ * hyper_flow_bound.hpp:44-76); CFL_Scenario / beta_Scenario: deeps2d_core.cpp:737-738 */
+enum { HF2D_T_CP = 0, HF2D_T_LAM = 4, HF2D_T_MU = 8, HF2D_T_CFL = 12, HF2D_T_BETA = 13 };
+
+typedef struct hf2d_cfg {
+    int    nx, ny;              /* MaxX, MaxY of this slab (ghost columns included when n_ranks > 1)        */
+    double dx, dy;              /* FlowNode2D::dx, dy                                                       */
+    double dt;                  /* initial dt = dt_min[0] at entry (deeps2d_core.cpp:660)                   */
+    double CFL, beta0, nrbc_beta0;
+    int    bFF;                 /* BlendingFactorFunction 0..5 (deeps2d_core.hpp:66-72)                     */
+    int    problem_type;        /* SolverMode: 0 SM_EULER, 1 SM_NS                                          */
+    int    flow_type;           /* FlowType: 0 FT_FLAT, 1 FT_AXISYMMETRIC                                   */
+    double Hu[4];               /* FlowNode2D::Hu                                                           */
+    int    TurbStartIter, TurbExtModel, isTurbulenceReset;
+    double SigW, SigF, delta_bl;
+    double turb_intensity;      /* FlowNodeTurbulence2D::I (0.005)                                          */
+    int    isAdiabaticWall, isAlternateRMS;
+    unsigned AddSrcStartIter;
+    unsigned last_iter;         /* global iteration count at entry                                          */
+    int    MonitorIndex;
+    double ExitMonitorValue;
+    double K0;                  /* chemical_reactions.K0                                                    */
+    double Rgas[4];             /* R_Fuel, R_OX, R_cp, R_air                                                */
+    hf2d_table tab[HF2D_NTABLES];
+    int    dt_rule;             /* 0 = serial running minimum (deeps2d_core.cpp:803,1326; the oracle's rule),
+                                   1 = per-step minimum (MPI build, :806-809,850)                           */
+    int    rank, n_ranks;       /* X-slab index / count; 0,1 for a single GPU                               */
+} hf2d_cfg;
+
+/* Byte offsets of the members of the caller's FlowNode2D record (offsetof on the reference's own header).
+ * int members (idXl..) are 4-byte ints, CT/TurbType 8-byte unsigned, everything else double.             */
+typedef struct hf2d_node_layout {
+    size_t node_bytes;
+    size_t S, dSdx, dSdy, TurbType, l_min, y_plus, mu_t, lam_t, dkdx, dkdy, depsdx, depsdy, y, p,
+           idXl, idYu, idXr, idYd, CT, beta, Q_conv, time, k, R, lam, mu, CP, Diff, Tf,
+           A, B, F, Src, SrcAdd, Tg, U, V, Y, Uw, Vw, droYdx, droYdy, dUdx, dUdy, dVdx, dVdy, dTdx, dTdy, BGX, BGY;
+} hf2d_node_layout;
+
+typedef struct hf2d_step_report {
+    double   dt;                 /* dt used by the last step                                               */
+    double   dt_min;             /* value the next step will use                                           */
+    double   time_part;          /* sum of dt over the steps of this call (CurrentTimePart, :1602)         */
+    double   sum_RMS[HF2D_NEQ];  /* residual norms of the last step (:1539-1574)                           */
+    double   max_RMS;
+    int      k_max_RMS;
+    double   DD_max[HF2D_NEQ];
+    unsigned iter;               /* global iteration count after the call                                  */
+    int      err, err_i, err_j;  /* Tg<0: first offending node in sweep order                              */
+    double   gpu_ms;             /* device time of the step loop (CUDA events)                             */
+    uint64_t kernel_launches;    /* kernels launched by this call                                          */
+} hf2d_step_report;
+
+typedef struct hf2d_gpu hf2d_gpu;   /* opaque handle */
+
+const char* hf2d_gpu_last_error(void);
+int  hf2d_gpu_device_count(void);
+
+/* Create a solver for one slab on CUDA device `device`.  Tables are copied. */
+int  hf2d_gpu_create(const hf2d_cfg* cfg, int device, hf2d_gpu** out);
+int  hf2d_gpu_destroy(hf2d_gpu* h);
+
+/* Host AoS grid image J[x*ny+y] -> SoA arrays in HBM (also (re)builds the boundary-node lists and zeroes the
+ * FlowNodeCore2D shadow exactly as hf2d_start.cpp:318 does).  `pinned` != 0 promises page-locked memory. */
+int  hf2d_gpu_upload_aos(hf2d_gpu* h, const void* J, const hf2d_node_layout* layout, int pinned);
+/* SoA arrays -> host AoS image; only members the step owns are written, everything else in J is left alone. */
+int  hf2d_gpu_download_aos(hf2d_gpu* h, void* J, const hf2d_node_layout* layout, int pinned);
+
+/* `nsteps` explicit time steps (one output cycle of the reference: iter = 0..nsteps-1 with last_iter fixed,
+ * isSrcAdd evaluated once at cycle start, deeps2d_core.cpp:727-731).  Asynchronous on the handle's stream
+ * until the report is read at the end.  `want_rms` = 0 skips the residual reduction read-back. */
+int  hf2d_gpu_step(hf2d_gpu* h, int nsteps, hf2d_step_report* report);
+
+/* One reference output cycle through host memory: upload + nsteps + download (what a shim that keeps J on the
+ * host between cycles does).  Used for the end-to-end metric. */
+int  hf2d_gpu_run_cycle(hf2d_gpu* h, void* J, const hf2d_node_layout* layout, int pinned, int nsteps,
+                        hf2d_step_report* report);
+
+/* Device-resident access for callers that keep the grid in HBM (benchmarks, multi-GPU drivers).
+ * name: "S","SN","beta","A","B","F","Src" (k = equation) or "U","V","Tg","p","k","R","CP","lam","mu","mu_t",
+ * "l_min","y_plus" (k = 0).  Returns the CURRENT device pointer of that plane (nx*ny doubles, x-major). */
+int  hf2d_gpu_field_ptr(hf2d_gpu* h, const char* name, int k, void** dev_ptr);
+int  hf2d_gpu_active_cells(hf2d_gpu* h, long long* n_active, long long* n_total);
+/* algorithmic bytes per active cell per step of the current configuration */
+int  hf2d_gpu_bytes_per_cell(hf2d_gpu* h, double* bytes);
+
+/* Multi-GPU (X-slabs, one process per GPU): pack the columns the neighbours need into `buf` / consume received
+ * ones.  side: 0 = left neighbour, 1 = right neighbour.  phase: 0 = before Stage 1, 1 = between the two halves
+ * of Stage 2 (see DESIGN.md "seams").  `buf` is device memory of hf2d_gpu_halo_bytes() bytes. */
+size_t hf2d_gpu_halo_bytes(hf2d_gpu* h, int phase);
+int  hf2d_gpu_halo_pack(hf2d_gpu* h, int side, int phase, void* dev_buf);
+int  hf2d_gpu_halo_unpack(hf2d_gpu* h, int side, int phase, const void* dev_buf);
+/* Split step for drivers that exchange halos between phases: begin (dt, scenario), stage1, stage2, end. */
+int  hf2d_gpu_step_begin(hf2d_gpu* h);
+int  hf2d_gpu_step_stage1(hf2d_gpu* h);
+int  hf2d_gpu_step_stage2(hf2d_gpu* h);
+int  hf2d_gpu_step_end(hf2d_gpu* h, hf2d_step_report* report /* may be NULL: no read-back */);
+/* dt of the running minimum as device pointer (one double) so a driver can all-reduce(min) it in place */
+int  hf2d_gpu_dt_ptr(hf2d_gpu* h, void** dev_ptr);
+void* hf2d_gpu_stream(hf2d_gpu* h);   /* cudaStream_t the handle launches on */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HF2D_GPU_H */

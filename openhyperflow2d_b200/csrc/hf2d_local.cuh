@@ -1,0 +1,138 @@
+// hf2d_local.cuh -- the part of Stage 2 that depends on a node's OWN data only.
+//
+// In the reference's in-place sweep (deeps2d_core.cpp:1028-1334) node C reads its left/down neighbours AFTER
+// they went through commit + FillNode2D + CalcChemicalReactions in this sweep and its right/up neighbours BEFORE
+// (SURVEY.md F4).  What a neighbour exposes (S[0], S[4..8], U, V, Tg) depends only on that neighbour's own
+// shadow S, flags and lagged CP/R -- never on gradients -- so any thread can recompute a neighbour's "new state"
+// with local_update() instead of waiting for it.  The same function is the first half of the node's own update.
+#pragma once
+#include "hf2d_dev.cuh"
+
+// pow(x, 3/2) of the k-eps boundary rewrites (hyper_flow_node.hpp:760,775,779)
+__device__ __forceinline__ double pow15(double x) { return pow(x, 1.5); }
+
+struct Local {
+    double S[NEQ];          // committed S after FillNode2D's local rewrites, BEFORE chemistry
+    double s7c, s8c;        // committed S[7], S[8] before TurbModRANS2D rewrote them
+    double U, V, Tg, p, kg; // after FillNode2D
+    double Uo, Vo, Tgo, po; // before (last step's)
+    double CP, R, mu;       // lagged properties (last step's chemistry)
+    double y4, y5, y6;      // S[4..6] after chemistry (what later nodes of the sweep read)
+    double Yfu, Yox, Ycp, Yair;   // mass fractions inside chemistry at the point where R/CP/lam/mu are formed
+    double Y[4];            // FlowNode2D::Y after chemistry
+    bool   filled;          // FillNode2D ran past its early returns
+    bool   active, fc;
+};
+
+// commit test of equation k (deeps2d_core.cpp:1156-1164)
+__device__ __forceinline__ bool eq_committed(uint32_t ct, uint32_t tt, int k, int ns) {
+    if (k < 4) return !is_set(ct, CT_Rho_CONST << k);
+    if (k < 4 + NCOMP) return !is_set(ct, CT_Y_CONST);
+    if (ns && (is_set(tt, TCT_k_eps_Model) || is_set(tt, TCT_SA_Model))) return !is_set(tt, TCT_k_CONST << (k - 4 - NCOMP));
+    return false;
+}
+
+// FULL=false computes only what neighbours read (S[0], S[4..8] post-chemistry, U, V, Tg).
+template <bool FULL>
+__device__ __forceinline__ void local_update(const Params& P, const StepState& st, long long m, uint32_t ct, uint32_t tt, Local& L) {
+    const long long N = P.N;
+    const bool act = node_active(ct);
+    const bool fc = !act && is_set(ct, NT_FC) && !is_set(ct, CT_SOLID);
+    L.active = act; L.fc = fc; L.filled = false;
+    const int ne = num_eq(tt);
+    const int nk = (P.ns && (tt & (TCT_k_eps_Model | TCT_SA_Model))) ? NEQ : 7;  // planes that can matter here
+    // ---- commit (active nodes only) ----
+#pragma unroll
+    for (int k = 0; k < NEQ; k++) {
+        double s = 0.;
+        if (k < 7 || k < nk) {
+            s = P.S_in[(long long)k * N + m];
+            if (act && k < ne && eq_committed(ct, tt, k, P.ns)) s = P.SN[(long long)k * N + m];
+        }
+        L.S[k] = s;
+    }
+    L.s7c = L.S[7]; L.s8c = L.S[8];
+    L.Uo = P.U_in[m]; L.Vo = P.V_in[m]; L.Tgo = P.Tg_in[m];
+    L.U = L.Uo; L.V = L.Vo; L.Tg = L.Tgo;
+    L.CP = P.CP_in[m]; L.R = P.R_in[m];
+    L.mu = P.ns ? P.mu_in[m] : 0.;
+    const double kg_old = P.kg[m];
+    L.kg = kg_old;
+    if (FULL) { L.po = P.p[m]; L.p = L.po; }
+    if (!act && !fc) { L.y4 = L.S[4]; L.y5 = L.S[5]; L.y6 = L.S[6]; return; }
+    // ---- FillNode2D, local part (hyper_flow_node.hpp:382-492) ----
+    if (!(L.S[iRho] == 0) && !(kg_old < 1)) {
+        L.filled = true;
+        L.kg = L.CP / (L.CP - L.R);
+        if (is_set(ct, CT_U_CONST)) L.S[iRhoU] = L.U * L.S[iRho]; else L.U = L.S[iRhoU] / L.S[iRho];
+        if (is_set(ct, CT_V_CONST)) L.S[iRhoV] = L.V * L.S[iRho]; else L.V = L.S[iRhoV] / L.S[iRho];
+        if (P.ns && (tt & TT_MASK) != 0) {
+            // the S-rewriting part of TurbModRANS2D (:753-779 k-eps, :856-862 SA)
+            if (is_set(tt, TCT_Prandtl_Model)) {
+            } else if (is_set(tt, TCT_k_eps_Model)) {
+                const double l = OMAX(P.l_min[m], OMIN(P.dy, P.dx)) * 0.41;
+                const double p34 = (P.tem == TEM_k_eps_RNG) ? P.pow_cmu_34[1] : P.pow_cmu_34[0];
+                if (st.is_init) {
+                    const double TmpI = P.turb_I * sqrt(L.U * L.U + L.V * L.V + 1.e-30);
+                    L.S[iK] = 1.5 * TmpI * TmpI * L.S[iRho];
+                    L.S[iEps] = p34 * pow15(L.S[iK] / L.S[iRho]) / l;
+                }
+                if (is_set(tt, TCT_k_CONST)) {
+                    const double TmpI = P.turb_I * sqrt(L.U * L.U + L.V * L.V + 1.e-30);
+                    L.S[iK] = 1.5 * TmpI * TmpI * L.S[iRho];
+                }
+                if (is_set(tt, TCT_eps_CONST)) L.S[iEps] = p34 * pow15(L.S[iK] / L.S[iRho]) / l;
+                if (is_set(tt, TCT_eps_Cmk2kXn_WALL)) L.S[iEps] = p34 * pow15(L.S[iK] / L.S[iRho]) / l;
+            } else if (is_set(tt, TCT_SA_Model)) {
+                if (st.is_init) L.S[iNut] = L.mu / L.S[iRho] / 100.0;
+                else if (is_set(ct, CT_WALL_NO_SLIP) || is_set(ct, CT_WALL_LAW) || is_set(tt, TCT_k_CONST)) L.S[iNut] = 0.;
+                else if (is_set(ct, NT_FC)) L.S[iNut] = L.mu / L.S[iRho] * P.turb_I;
+            }
+        }
+        double Tmp1 = L.S[iRho], Tmp3 = 0.;
+#pragma unroll
+        for (int i = 0; i < NCOMP; i++) { Tmp3 += P.Hu[i] * L.S[i + 4]; Tmp1 -= L.S[i + 4]; }
+        Tmp3 += P.Hu[NCOMP] * Tmp1;
+        if (is_set(ct, CT_WALL_LAW)) {
+            const SpecNode& sp = P.spec[P.spec_idx[m]];
+            Tmp1 = sqrt(L.U * L.U + L.V * L.V + 1.e-30);
+            L.S[iRhoU] = Tmp1 * sp.BGX;
+            L.S[iRhoV] = Tmp1 * sp.BGY;
+            L.U = L.S[iRhoU] / L.S[iRho];
+            L.V = L.S[iRhoV] / L.S[iRho];
+        } else if (is_set(ct, CT_WALL_NO_SLIP)) {
+            const SpecNode& sp = P.spec[P.spec_idx[m]];
+            L.U = sp.Uw; L.V = sp.Vw;
+            L.S[iRhoU] = L.U * L.S[iRho];
+            L.S[iRhoV] = L.V * L.S[iRho];
+        }
+        const double pp = (L.kg - 1.) * (L.S[iRhoE] - L.S[iRho] * (L.U * L.U + L.V * L.V) * 0.5 - Tmp3);
+        L.Tg = pp / L.R / L.S[iRho];
+        if (FULL) L.p = pp;
+    }
+    // ---- species part of CalcChemicalReactions (deeps2d_core.cpp:4702-4728, 4748-4777); active nodes only ----
+    L.y4 = L.S[4]; L.y5 = L.S[5]; L.y6 = L.S[6];
+    if (act) {
+        double Yfu = L.S[iYfu] / L.S[0], Yox = L.S[iYox] / L.S[0], Ycp = L.S[iYcp] / L.S[0];
+        double Yair = 1. - (Yfu + Yox + Ycp);
+        const bool yconst = is_set(ct, CT_Y_CONST);
+        if (!yconst) {
+            double Y0 = 1. / (Yfu + Yox + Ycp + Yair);
+            Yfu = Yfu * Y0; Yox = Yox * Y0; Ycp = Ycp * Y0;
+            const double Tf = P.tf_uniform ? P.Tf0 : P.Tf[m];
+            if (L.Tg > Tf) {
+                if (Yox > Yfu * P.K0) { Yox = Yox - Yfu * P.K0; Yfu = 0.; Ycp = 1. - Yox - Yair; }
+                else { Yfu = Yfu - Yox / P.K0; Yox = 0.; Ycp = 1. - Yfu - Yair; }
+            }
+        }
+        if (FULL) { L.Yfu = Yfu; L.Yox = Yox; L.Ycp = Ycp; L.Yair = Yair; }
+        if (Yair < 1.e-5) Yair = 0.;
+        if (Ycp < 1.e-8) Ycp = 0.;
+        if (Yox < 1.e-8) Yox = 0.;
+        if (Yfu < 1.e-8) Yfu = 0.;
+        const double Y0 = 1. / (Yfu + Yox + Ycp + Yair);
+        Yfu = Yfu * Y0; Yox = Yox * Y0; Ycp = Ycp * Y0; Yair = Yair * Y0;
+        if (FULL) { L.Y[0] = Yfu; L.Y[1] = Yox; L.Y[2] = Ycp; L.Y[3] = Yair; }
+        if (!yconst) { L.y4 = fabs(Yfu * L.S[0]); L.y5 = fabs(Yox * L.S[0]); L.y6 = fabs(Ycp * L.S[0]); }
+    }
+}

@@ -1,0 +1,169 @@
+// hf2d_stage1.cuh -- Stage 1 of the DEEPS2D step (deeps2d_core.cpp:853-1026) as parallel kernels.
+//
+// The reference sweeps i-outer/j-inner IN PLACE: a node with a d/dx=0 or d/dy=0 flag overwrites its own S[k]
+// from its neighbours before the update, and nodes visited later see the overwritten value while nodes visited
+// earlier saw the old one.  Parallel-exact restatement:
+//   k_neumann_save   : copy S of every Neumann-list node into its SpecNode::S0            (old values)
+//   k_neumann_level  : level by level (level = longest chain of Neumann nodes through left/down neighbours)
+//                      apply the overwrite in place, reading left/down from the array (already new) and
+//                      right/up through S0 when that neighbour is itself a list node (still old)
+//   k_stage1         : every node: own/left/down S from the array (new), right/up S through S0 if listed (old)
+#pragma once
+#include "hf2d_dev.cuh"
+
+__global__ void k_begin_step(Params P) {
+    // one thread: dt for this step, scenario tables, FillNode2D mode flags; clears the residual accumulators
+    StepState* s = P.st;
+    const double dtm = bits2d(s->dt_min_bits);
+    s->dt = dtm;                                                     // deeps2d_core.cpp:803 (serial rule)
+    if (P.dt_rule == 1) s->dt_min_bits = d2bits(1.0);               // MPI rule: per-step minimum (:850)
+    const double it = (double)s->iter;
+    s->beta_scn = tab_get(&P.tab[13], it);
+    s->CFL_scn = tab_get(&P.tab[12], it);
+    if ((int)s->iter < P.TurbStartIter) { s->is_mu_t = 0; s->is_init = P.isTurbulenceReset; }
+    else { s->is_mu_t = 1; s->is_init = 0; }
+    for (int k = 0; k < NEQ; k++) { s->RMS[k] = 0.; s->sumDiv[k] = 0.; s->iRMS[k] = 0ull; s->DDmax_bits[k] = 0ull; }
+    s->block_counter = 0;
+}
+
+__global__ void k_end_step(Params P) {
+    StepState* s = P.st;
+    s->time_part += s->dt;                                           // CurrentTimePart += dt, :1602
+    s->iter += 1;
+}
+
+__global__ void k_neumann_save(Params P, const int* __restrict__ list, int n_list) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_list) return;
+    SpecNode& sp = P.spec[list[t]];
+    const long long n = sp.node;
+#pragma unroll
+    for (int k = 0; k < NEQ; k++) sp.S0[k] = P.S_in[(long long)k * P.N + n];
+}
+
+// S of neighbour m as a node AHEAD of it in the sweep sees it: the pre-overwrite value
+__device__ __forceinline__ double s_old(const Params& P, long long m, uint32_t tt_m, int k) {
+    if (tt_m & TT_NLIST) return P.spec[P.spec_idx[m]].S0[k];
+    return P.S_in[(long long)k * P.N + m];
+}
+
+__global__ void k_neumann_level(Params P, const int* __restrict__ list, int first, int count) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= count) return;
+    const SpecNode& sp = P.spec[list[first + t]];
+    const long long n = sp.node, ny = P.ny, N = P.N;
+    const uint32_t ct = P.ct[n], tt = P.tt[n];
+    const int n1 = (tt & TT_IDXL) ? 1 : 0, n2 = (tt & TT_IDXR) ? 1 : 0, n3 = (tt & TT_IDYU) ? 1 : 0, n4 = (tt & TT_IDYD) ? 1 : 0;
+    const long long nL = n - n1 * ny, nR = n + n2 * ny, nU = n + n3, nD = n - n4;
+    const double n_n = OMAX(n1 + n2, 1), m_m = OMAX(n3 + n4, 1);
+    const double n_n_1 = 1. / n_n, m_m_1 = 1. / m_m;
+    const uint32_t ttR = P.tt[nR], ttU = P.tt[nU];
+    const int ne = num_eq(tt);
+    for (int k = 0; k < ne; k++) {
+        const unsigned f = eq_flags(ct, tt, k, P.ns);
+        if (!(f & 1)) continue;
+        double* Sk = P.S_in + (long long)k * N;
+        double sc = Sk[n];
+        bool wr = false;
+        if (!(f & 2)) {   // :998  (weights are crossed in x: left*n2 + right*n1)
+            const double sl = n1 ? Sk[nL] : sc;
+            const double sr = n2 ? s_old(P, nR, ttR, k) : sc;
+            sc = (sl * n2 + sr * n1) * n_n_1;
+            wr = true;
+        }
+        if (!(f & 4)) {   // :1005
+            const double su = n3 ? s_old(P, nU, ttU, k) : sc;
+            const double sd = n4 ? Sk[nD] : sc;
+            sc = (su * n3 + sd * n4) * m_m_1;
+            wr = true;
+        }
+        if (wr) Sk[n] = sc;
+    }
+}
+
+// this-sweep value of dSdx[k] (dir 0) / dSdy[k] (dir 1) of node m, for soft-BC readers behind it in the sweep
+__device__ __forceinline__ double ds_new(const Params& P, long long m, int k, int dir) {
+    const uint32_t ct = P.ct[m], tt = P.tt[m];
+    const double* oldp = dir ? P.dSy_in[k] : P.dSx_in[k];
+    if (!node_active(ct) || k >= num_eq(tt)) return oldp[m];
+    const unsigned f = eq_flags(ct, tt, k, P.ns);
+    if (!(f & 1)) return oldp[m];
+    if (dir == 0) {
+        if (!(f & 2)) return 0.;
+        const int n1 = (tt & TT_IDXL) ? 1 : 0, n2 = (tt & TT_IDXR) ? 1 : 0;
+        const double n_n_1 = 1. / (double)OMAX(n1 + n2, 1);
+        const double* Ak = P.A + (long long)k * P.N;
+        return (Ak[m + n2 * (long long)P.ny] - Ak[m - n1 * (long long)P.ny]) * n_n_1;
+    } else {
+        if (!(f & 4)) return 0.;
+        const int n3 = (tt & TT_IDYU) ? 1 : 0, n4 = (tt & TT_IDYD) ? 1 : 0;
+        const double m_m_1 = 1. / (double)OMAX(n3 + n4, 1);
+        const double* Bk = P.B + (long long)k * P.N;
+        return (Bk[m + n3] - Bk[m - n4]) * m_m_1;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_stage1(Params P) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int i = P.i_lo + blockIdx.y * blockDim.y + threadIdx.y;
+    if (j >= P.ny || i >= P.i_hi) return;
+    const long long ny = P.ny, N = P.N, n = (long long)i * ny + j;
+    const uint32_t ct = P.ct[n], tt = P.tt[n];
+    const bool act = node_active(ct);
+    const int ne = act ? num_eq(tt) : 0;
+    // tracked dS planes must be carried over for nodes / equations that are not advanced
+    if (P.need_dsx | P.need_dsy) {
+        for (int k = 0; k < NEQ; k++) {
+            const bool adv = act && k < ne && (eq_flags(ct, tt, k, P.ns) & 1);
+            if (!adv) {
+                if (P.need_dsx & (1u << k)) P.dSx_out[k][n] = P.dSx_in[k][n];
+                if (P.need_dsy & (1u << k)) P.dSy_out[k][n] = P.dSy_in[k][n];
+            }
+        }
+    }
+    if (!act) return;
+    const int n1 = (tt & TT_IDXL) ? 1 : 0, n2 = (tt & TT_IDXR) ? 1 : 0, n3 = (tt & TT_IDYU) ? 1 : 0, n4 = (tt & TT_IDYD) ? 1 : 0;
+    const long long nL = n - n1 * ny, nR = n + n2 * ny, nU = n + n3, nD = n - n4;
+    const double n_n = OMAX(n1 + n2, 1), m_m = OMAX(n3 + n4, 1);
+    const double n_n_1 = 1. / n_n, m_m_1 = 1. / m_m;
+    const uint32_t ttR = n2 ? P.tt[nR] : 0u, ttU = n3 ? P.tt[nU] : 0u;
+    const double dt = P.st->dt;
+    const double dtdx = dt / P.dx, dtdy = dt / P.dy;                  // :843-844
+    const double dyy = P.dx / (P.dx + P.dy), dxx = P.dy / (P.dx + P.dy);   // :643-644
+    const SpecNode* sp = (tt & TT_SPEC) ? &P.spec[P.spec_idx[n]] : nullptr;
+    for (int k = 0; k < ne; k++) {
+        const unsigned f = eq_flags(ct, tt, k, P.ns);
+        if (!(f & 1)) continue;
+        const long long o = (long long)k * N;
+        const double beta = P.beta[o + n], _beta = 1. - beta;
+        const double sc = P.S_in[o + n];
+        const double sl = P.S_in[o + nL], sd = P.S_in[o + nD];
+        const double sr = n2 ? s_old(P, nR, ttR, k) : sc;
+        const double su = n3 ? s_old(P, nU, ttU, k) : sc;
+        double dXX, dYY;
+        if (f & 2) dXX = (P.A[o + nR] - P.A[o + nL]) * n_n_1; else dXX = 0.;
+        if (f & 4) dYY = (P.B[o + nU] - P.B[o + nD]) * m_m_1; else dYY = 0.;
+        if (P.need_dsx & (1u << k)) P.dSx_out[k][n] = dXX;
+        if (P.need_dsy & (1u << k)) P.dSy_out[k][n] = dYY;
+        if (f & 8) {    // :1008-1010  left: this sweep's value, right: last step's (own value if aliased)
+            const double dl = n1 ? ds_new(P, nL, k, 0) : dXX;
+            const double dr = n2 ? P.dSx_in[k][nR] : dXX;
+            dXX = (dl + dr) * 0.5;
+        }
+        if (f & 16) {   // :1011-1013
+            const double du = n3 ? P.dSy_in[k][nU] : dYY;
+            const double dd = n4 ? ds_new(P, nD, k, 1) : dYY;
+            dYY = (du + dd) * 0.5;
+        }
+        double src = 0.;
+        if (k >= 7 || P.has_src) src = P.Src[o + n];
+        const double srcadd = sp ? sp->SrcAdd[k] : 0.;
+        double sn;
+        if (P.axi) {
+            sn = sc * beta + _beta * (dxx * (sl + sr) + dyy * (su + sd)) * 0.5 - (dtdx * dXX + dtdy * (dYY + P.F[o + n] / (j + 1))) + src * dt + srcadd;
+        } else {
+            sn = sc * beta + _beta * (dxx * (sl + sr) + dyy * (su + sd)) * 0.5 - (dtdx * dXX + dtdy * dYY) + src * dt + srcadd;
+        }
+        P.SN[o + n] = sn;
+    }
+}
