@@ -1,0 +1,47 @@
+"""Build libhf2d_gpu.so (the C-ABI shared library with the sm_100a kernels) in-tree with nvcc.
+
+-fmad=false: the parity contract is the reference compiled for x86-64 without FMA contraction; IEEE division and
+square root are nvcc's default for double.  -lineinfo so ncu's source page maps to the .cuh files."""
+from __future__ import annotations
+
+import os
+import shutil
+import subprocess
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+SO = os.path.join(HERE, "libhf2d_gpu.so")
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-fmad=false", "-std=c++17",
+              "-shared", "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
+
+
+def _newest_src() -> float:
+    t = 0.0
+    for root in (CSRC, os.path.join(os.path.dirname(HERE), "include")):
+        for f in os.listdir(root):
+            t = max(t, os.path.getmtime(os.path.join(root, f)))
+    return t
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    if not force and os.path.exists(SO) and os.path.getmtime(SO) >= _newest_src():
+        return SO
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(nvcc):
+        if os.path.exists(SO):
+            return SO   # GPU box without a toolchain: use the prebuilt library that travelled with the snapshot
+        raise RuntimeError("nvcc not found and no prebuilt libhf2d_gpu.so")
+    cmd = [nvcc] + NVCC_FLAGS + ["-o", SO, os.path.join(CSRC, "hf2d_gpu.cu")]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    log = r.stdout + r.stderr
+    with open(os.path.join(HERE, "build.log"), "w") as f:
+        f.write(" ".join(cmd) + "\n" + log)
+    if verbose:
+        print(log)
+    if r.returncode != 0:
+        raise RuntimeError("nvcc failed:\n" + log[-4000:])
+    return SO
+
+
+if __name__ == "__main__":
+    print(build(force=True, verbose=True))

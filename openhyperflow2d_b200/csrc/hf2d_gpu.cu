@@ -1,0 +1,124 @@
+// hf2d_gpu.cu -- C ABI of the B200-native DEEPS2D step (include/hf2d_gpu.h) and the host side of the step loop.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -fmad=false -shared -Xcompiler -fPIC
+//        (-fmad=false: the parity contract is the x86-64 reference built without FMA contraction).
+#include "../../include/hf2d_gpu.h"
+#include "hf2d_dev.cuh"
+#include "hf2d_stage1.cuh"
+#include "hf2d_stage2.cuh"
+#include "hf2d_heat.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+static thread_local char g_err[512] = "";
+static int fail(int code, const char* fmt, ...) {
+    va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof(g_err), fmt, ap); va_end(ap);
+    return code;
+}
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(HF2D_ECUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); } while (0)
+
+struct hf2d_gpu {
+    hf2d_cfg cfg;
+    int device;
+    cudaStream_t stream;
+    cudaEvent_t ev0, ev1;
+    Params P;                       // device pointers + configuration, passed by value to the kernels
+    std::vector<void*> allocs;
+    DevTable* d_tab;
+    StepState* d_st;
+    StepState* h_st;                // pinned mirror
+    bool uploaded;
+    int n_used_eq;                  // 7, 8 or 9: highest equation any node advances
+    // boundary lists (indices into spec[])
+    std::vector<SpecNode> h_spec;
+    std::vector<int> h_spec_idx_nodes;
+    int *d_nlist, *d_wall_list;
+    int n_nlist, n_wall;
+    std::vector<int> level_first, level_count;
+    long long n_active;
+    unsigned last_iter_cycle;       // last_iter of the reference (fixed during one cycle)
+    uint64_t launches;
+    void* d_stage; size_t stage_bytes;
+    double bytes_per_cell;
+};
+
+extern "C" const char* hf2d_gpu_last_error(void) { return g_err; }
+extern "C" int hf2d_gpu_device_count(void) { int n = 0; if (cudaGetDeviceCount(&n) != cudaSuccess) return 0; return n; }
+
+template <class T> static int dalloc(hf2d_gpu* h, T** p, size_t count, bool zero = true) {
+    void* q = nullptr;
+    CK(cudaMalloc(&q, std::max<size_t>(count, 1) * sizeof(T)));
+    if (zero) CK(cudaMemsetAsync(q, 0, std::max<size_t>(count, 1) * sizeof(T), h->stream));
+    h->allocs.push_back(q);
+    *p = (T*)q;
+    return 0;
+}
+
+extern "C" int hf2d_gpu_create(const hf2d_cfg* cfg, int device, hf2d_gpu** out) {
+    if (!cfg || !out) return fail(HF2D_EINVAL, "null argument");
+    if (cfg->nx < 1 || cfg->ny < 1) return fail(HF2D_EINVAL, "bad grid %d x %d", cfg->nx, cfg->ny);
+    if (cfg->bFF < 0 || cfg->bFF > 5) return fail(HF2D_EINVAL, "BFF %d is not implemented by the reference step (0..5)", cfg->bFF);
+    for (int t = 0; t < HF2D_NTABLES; t++)
+        if (cfg->tab[t].n > MAX_TAB_ROWS || cfg->tab[t].n < 0) return fail(HF2D_EINVAL, "table %d has %d rows (max %d)", t, cfg->tab[t].n, MAX_TAB_ROWS);
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(HF2D_ECUDA, "no CUDA device: this library has no CPU fallback");
+    if (device < 0 || device >= ndev) return fail(HF2D_EINVAL, "device %d out of range (%d devices)", device, ndev);
+    CK(cudaSetDevice(device));
+    hf2d_gpu* h = new hf2d_gpu();
+    h->cfg = *cfg; h->device = device; h->uploaded = false; h->launches = 0; h->d_stage = nullptr; h->stage_bytes = 0;
+    h->d_nlist = h->d_wall_list = nullptr; h->n_nlist = h->n_wall = 0; h->n_active = 0;
+    for (int t = 0; t < HF2D_NTABLES; t++) { h->cfg.tab[t].x = nullptr; h->cfg.tab[t].y = nullptr; }
+    CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    CK(cudaEventCreate(&h->ev0)); CK(cudaEventCreate(&h->ev1));
+    std::vector<DevTable> tabs(HF2D_NTABLES);
+    for (int t = 0; t < HF2D_NTABLES; t++) {
+        memset(&tabs[t], 0, sizeof(DevTable));
+        tabs[t].n = cfg->tab[t].n;
+        for (int r = 0; r < cfg->tab[t].n; r++) { tabs[t].x[r] = cfg->tab[t].x[r]; tabs[t].y[r] = cfg->tab[t].y[r]; }
+    }
+    if (dalloc(h, &h->d_tab, HF2D_NTABLES)) return HF2D_ECUDA;
+    CK(cudaMemcpyAsync(h->d_tab, tabs.data(), sizeof(DevTable) * HF2D_NTABLES, cudaMemcpyHostToDevice, h->stream));
+    if (dalloc(h, &h->d_st, 1)) return HF2D_ECUDA;
+    CK(cudaMallocHost((void**)&h->h_st, sizeof(StepState)));
+    CK(cudaStreamSynchronize(h->stream));
+    Params& P = h->P;
+    memset(&P, 0, sizeof(P));
+    P.nx = cfg->nx; P.ny = cfg->ny; P.N = (long long)cfg->nx * cfg->ny;
+    // sweep range of this slab (deeps2d_core.cpp:831-840): ghost columns are not swept
+    P.i_lo = (cfg->n_ranks > 1 && cfg->rank > 0) ? 1 : 0;
+    P.i_hi = (cfg->n_ranks > 1 && cfg->rank < cfg->n_ranks - 1) ? cfg->nx - 1 : cfg->nx;
+    P.dx = cfg->dx; P.dy = cfg->dy; P.CFL = cfg->CFL; P.beta0 = cfg->beta0; P.nrbc_beta0 = cfg->nrbc_beta0;
+    P.bFF = cfg->bFF; P.ns = cfg->problem_type == 1; P.axi = cfg->flow_type == 1;
+    for (int q = 0; q < 4; q++) { P.Hu[q] = cfg->Hu[q]; P.Rgas[q] = cfg->Rgas[q]; }
+    P.TurbStartIter = cfg->TurbStartIter; P.tem = cfg->TurbExtModel; P.isTurbulenceReset = cfg->isTurbulenceReset;
+    P.SigW = cfg->SigW; P.SigF = cfg->SigF; P.delta_bl = cfg->delta_bl; P.turb_I = cfg->turb_intensity;
+    P.isAdiabaticWall = cfg->isAdiabaticWall; P.isAlternateRMS = cfg->isAlternateRMS;
+    P.K0 = cfg->K0; P.dt_rule = cfg->dt_rule;
+    // pow(C_mu, 3/4) is a constant of the model: evaluate it with the host libm the reference links against
+    P.pow_cmu_34[0] = pow(0.09, 3. / 4.); P.pow_cmu_34[1] = pow(0.0845, 3. / 4.);
+    P.tab = h->d_tab; P.st = h->d_st;
+    h->last_iter_cycle = cfg->last_iter;
+    *out = h;
+    return HF2D_OK;
+}
+
+extern "C" int hf2d_gpu_destroy(hf2d_gpu* h) {
+    if (!h) return HF2D_OK;
+    cudaSetDevice(h->device);
+    cudaStreamSynchronize(h->stream);
+    for (void* p : h->allocs) cudaFree(p);
+    if (h->d_stage) cudaFree(h->d_stage);
+    if (h->h_st) cudaFreeHost(h->h_st);
+    cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
+    cudaStreamDestroy(h->stream);
+    delete h;
+    return HF2D_OK;
+}
+
+#include "hf2d_io.inc"
+#include "hf2d_step.inc"

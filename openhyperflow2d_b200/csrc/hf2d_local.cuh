@@ -20,6 +20,7 @@ struct Local {
     double y4, y5, y6;      // S[4..6] after chemistry (what later nodes of the sweep read)
     double Yfu, Yox, Ycp, Yair;   // mass fractions inside chemistry at the point where R/CP/lam/mu are formed
     double Y[4];            // FlowNode2D::Y after chemistry
+    double Upre, Vpre;      // S[RhoU]/S[Rho], S[RhoV]/S[Rho] of a no-slip wall node before the wall reset (virtual sources)
     bool   filled;          // FillNode2D ran past its early returns
     bool   active, fc;
 };
@@ -102,6 +103,7 @@ __device__ __forceinline__ void local_update(const Params& P, const StepState& s
             L.V = L.S[iRhoV] / L.S[iRho];
         } else if (is_set(ct, CT_WALL_NO_SLIP)) {
             const SpecNode& sp = P.spec[P.spec_idx[m]];
+            if (FULL) { L.Upre = L.S[iRhoU] / L.S[iRho]; L.Vpre = L.S[iRhoV] / L.S[iRho]; }
             L.U = sp.Uw; L.V = sp.Vw;
             L.S[iRhoU] = L.U * L.S[iRho];
             L.S[iRhoV] = L.V * L.S[iRho];
