@@ -1,0 +1,196 @@
+"""ctypes binding of include/hf2d_gpu.h (libhf2d_gpu.so) -- the Python mirror of the reference-side shim.
+
+Host language note: the reference is C++; its toolchain (g++) is present, but the reference has no FFI of its own,
+so the seam is the C ABI in include/hf2d_gpu.h.  INTEGRATION.md shows the C++ shim a maintainer adds to
+DEEPS2D_Run; this module is the same thing for Python callers (tests, bench) and never touches oracle/.
+There is NO CPU fallback: every call fails loudly if the CUDA library is missing or no device is present.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import build as _build
+from .config import TABLE_ORDER
+
+NEQ, NTAB = 9, 14
+
+LAYOUT_FIELDS = ["S", "dSdx", "dSdy", "TurbType", "l_min", "y_plus", "mu_t", "lam_t", "dkdx", "dkdy", "depsdx", "depsdy", "y", "p",
+                 "idXl", "idYu", "idXr", "idYd", "CT", "beta", "Q_conv", "time", "k", "R", "lam", "mu", "CP", "Diff", "Tf",
+                 "A", "B", "F", "Src", "SrcAdd", "Tg", "U", "V", "Y", "Uw", "Vw", "droYdx", "droYdy", "dUdx", "dUdy", "dVdx", "dVdy",
+                 "dTdx", "dTdy", "BGX", "BGY"]
+
+
+class Table(C.Structure):
+    _fields_ = [("n", C.c_int), ("x", C.POINTER(C.c_double)), ("y", C.POINTER(C.c_double))]
+
+
+class Cfg(C.Structure):
+    _fields_ = [
+        ("nx", C.c_int), ("ny", C.c_int), ("dx", C.c_double), ("dy", C.c_double), ("dt", C.c_double),
+        ("CFL", C.c_double), ("beta0", C.c_double), ("nrbc_beta0", C.c_double),
+        ("bFF", C.c_int), ("problem_type", C.c_int), ("flow_type", C.c_int), ("Hu", C.c_double * 4),
+        ("TurbStartIter", C.c_int), ("TurbExtModel", C.c_int), ("isTurbulenceReset", C.c_int),
+        ("SigW", C.c_double), ("SigF", C.c_double), ("delta_bl", C.c_double), ("turb_intensity", C.c_double),
+        ("isAdiabaticWall", C.c_int), ("isAlternateRMS", C.c_int), ("AddSrcStartIter", C.c_uint), ("last_iter", C.c_uint),
+        ("MonitorIndex", C.c_int), ("ExitMonitorValue", C.c_double), ("K0", C.c_double), ("Rgas", C.c_double * 4),
+        ("tab", Table * NTAB), ("dt_rule", C.c_int), ("rank", C.c_int), ("n_ranks", C.c_int),
+    ]
+
+
+class NodeLayout(C.Structure):
+    _fields_ = [("node_bytes", C.c_size_t)] + [(f, C.c_size_t) for f in LAYOUT_FIELDS]
+
+
+class StepReport(C.Structure):
+    _fields_ = [
+        ("dt", C.c_double), ("dt_min", C.c_double), ("time_part", C.c_double), ("sum_RMS", C.c_double * NEQ),
+        ("max_RMS", C.c_double), ("k_max_RMS", C.c_int), ("DD_max", C.c_double * NEQ), ("iter", C.c_uint),
+        ("err", C.c_int), ("err_i", C.c_int), ("err_j", C.c_int), ("gpu_ms", C.c_double), ("kernel_launches", C.c_uint64),
+    ]
+
+
+class Hf2dError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"hf2d_gpu error {code}: {msg}")
+        self.code = code
+
+
+_lib = None
+EXPORTS = ["hf2d_gpu_last_error", "hf2d_gpu_device_count", "hf2d_gpu_create", "hf2d_gpu_destroy", "hf2d_gpu_upload_aos",
+           "hf2d_gpu_download_aos", "hf2d_gpu_step", "hf2d_gpu_run_cycle", "hf2d_gpu_field_ptr", "hf2d_gpu_active_cells",
+           "hf2d_gpu_bytes_per_cell", "hf2d_gpu_halo_bytes", "hf2d_gpu_halo_pack", "hf2d_gpu_halo_unpack", "hf2d_gpu_step_begin",
+           "hf2d_gpu_step_stage1", "hf2d_gpu_step_stage2", "hf2d_gpu_step_end", "hf2d_gpu_dt_ptr", "hf2d_gpu_stream"]
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        so = _build.build()
+        L = C.CDLL(so)
+        L.hf2d_gpu_last_error.restype = C.c_char_p
+        L.hf2d_gpu_create.argtypes = [C.POINTER(Cfg), C.c_int, C.POINTER(C.c_void_p)]
+        L.hf2d_gpu_destroy.argtypes = [C.c_void_p]
+        L.hf2d_gpu_upload_aos.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(NodeLayout), C.c_int]
+        L.hf2d_gpu_download_aos.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(NodeLayout), C.c_int]
+        L.hf2d_gpu_step.argtypes = [C.c_void_p, C.c_int, C.POINTER(StepReport)]
+        L.hf2d_gpu_run_cycle.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(NodeLayout), C.c_int, C.c_int, C.POINTER(StepReport)]
+        L.hf2d_gpu_field_ptr.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.POINTER(C.c_void_p)]
+        L.hf2d_gpu_active_cells.argtypes = [C.c_void_p, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]
+        L.hf2d_gpu_bytes_per_cell.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+        L.hf2d_gpu_halo_bytes.argtypes = [C.c_void_p, C.c_int]
+        L.hf2d_gpu_halo_bytes.restype = C.c_size_t
+        L.hf2d_gpu_halo_pack.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.hf2d_gpu_halo_unpack.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        for f in ("hf2d_gpu_step_begin", "hf2d_gpu_step_stage1", "hf2d_gpu_step_stage2"):
+            getattr(L, f).argtypes = [C.c_void_p]
+        L.hf2d_gpu_step_end.argtypes = [C.c_void_p, C.POINTER(StepReport)]
+        L.hf2d_gpu_dt_ptr.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
+        L.hf2d_gpu_stream.argtypes = [C.c_void_p]
+        L.hf2d_gpu_stream.restype = C.c_void_p
+        _lib = L
+    return _lib
+
+
+def _ck(rc):
+    if rc != 0:
+        raise Hf2dError(rc, lib().hf2d_gpu_last_error().decode())
+
+
+def make_layout(layout: dict) -> NodeLayout:
+    nl = NodeLayout()
+    nl.node_bytes = layout["node_bytes"]
+    for f in LAYOUT_FIELDS:
+        setattr(nl, f, layout["fields"][f][0])
+    return nl
+
+
+def make_cfg(cfg: dict, nx=None, ny=None, rank=0, n_ranks=1, dt_rule=0):
+    c = Cfg()
+    keep = []
+    c.nx, c.ny = nx or cfg["MaxX"], ny or cfg["MaxY"]
+    c.dx, c.dy, c.dt = cfg["dx"], cfg["dy"], cfg["dt"]
+    c.CFL, c.beta0, c.nrbc_beta0 = cfg["CFL"], cfg["beta0"], cfg["nrbc_beta0"]
+    c.bFF, c.problem_type, c.flow_type = cfg["bFF"], cfg["ProblemType"], cfg["FT"]
+    for i in range(4):
+        c.Hu[i] = cfg["Hu"][i]
+    c.TurbStartIter, c.TurbExtModel, c.isTurbulenceReset = cfg["TurbStartIter"], cfg["TurbExtModel"], cfg["isTurbulenceReset"]
+    c.SigW, c.SigF, c.delta_bl, c.turb_intensity = cfg["SigW"], cfg["SigF"], cfg["delta_bl"], cfg.get("TurbIntensity", 0.005)
+    c.isAdiabaticWall, c.isAlternateRMS = cfg["isAdiabaticWall"], cfg["isAlternateRMS"]
+    c.AddSrcStartIter, c.last_iter = cfg.get("AddSrcStartIter", 0), cfg.get("last_iter", 0)
+    c.MonitorIndex, c.ExitMonitorValue, c.K0 = cfg.get("MonitorIndex", 5), cfg.get("ExitMonitorValue", 0.0), cfg["K0"]
+    for i, k in enumerate(["R_Fuel", "R_OX", "R_cp", "R_air"]):
+        c.Rgas[i] = cfg[k]
+    for i, name in enumerate(TABLE_ORDER):
+        x, y = cfg["tables"].get(name, ([], []))
+        xa = (C.c_double * max(len(x), 1))(*x)
+        ya = (C.c_double * max(len(y), 1))(*y)
+        keep += [xa, ya]
+        c.tab[i].n = len(x)
+        c.tab[i].x = C.cast(xa, C.POINTER(C.c_double))
+        c.tab[i].y = C.cast(ya, C.POINTER(C.c_double))
+    c.dt_rule, c.rank, c.n_ranks = dt_rule, rank, n_ranks
+    return c, keep
+
+
+class Solver:
+    """One X-slab of the DEEPS2D step on one GPU (hf2d_gpu handle)."""
+
+    def __init__(self, cfg: dict, layout: dict, device: int = 0, **kw):
+        self._h = C.c_void_p()
+        self.cfg = cfg
+        self.layout = make_layout(layout)
+        c, self._keep = make_cfg(cfg, **kw)
+        self.nx, self.ny = c.nx, c.ny
+        _ck(lib().hf2d_gpu_create(C.byref(c), device, C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            lib().hf2d_gpu_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @staticmethod
+    def _ptr(J):
+        if isinstance(J, np.ndarray):
+            assert J.flags.c_contiguous
+            return J.ctypes.data
+        return int(J)
+
+    def upload_aos(self, J, pinned=False):
+        _ck(lib().hf2d_gpu_upload_aos(self._h, self._ptr(J), C.byref(self.layout), int(pinned)))
+
+    def download_aos(self, J, pinned=False):
+        _ck(lib().hf2d_gpu_download_aos(self._h, self._ptr(J), C.byref(self.layout), int(pinned)))
+
+    def step(self, nsteps: int) -> StepReport:
+        rep = StepReport()
+        _ck(lib().hf2d_gpu_step(self._h, nsteps, C.byref(rep)))
+        return rep
+
+    def run_cycle(self, J, nsteps: int, pinned=False) -> StepReport:
+        rep = StepReport()
+        _ck(lib().hf2d_gpu_run_cycle(self._h, self._ptr(J), C.byref(self.layout), int(pinned), nsteps, C.byref(rep)))
+        return rep
+
+    def field_ptr(self, name: str, k: int = 0) -> int:
+        p = C.c_void_p()
+        _ck(lib().hf2d_gpu_field_ptr(self._h, name.encode(), k, C.byref(p)))
+        return p.value
+
+    def active_cells(self):
+        a, t = C.c_longlong(), C.c_longlong()
+        _ck(lib().hf2d_gpu_active_cells(self._h, C.byref(a), C.byref(t)))
+        return a.value, t.value
+
+    def bytes_per_cell(self) -> float:
+        b = C.c_double()
+        _ck(lib().hf2d_gpu_bytes_per_cell(self._h, C.byref(b)))
+        return b.value
