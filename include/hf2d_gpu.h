@@ -138,6 +138,10 @@ int  hf2d_gpu_step_end(hf2d_gpu* h, hf2d_step_report* report /* may be NULL: no 
 /* dt of the running minimum as device pointer (one double) so a driver can all-reduce(min) it in place */
 int  hf2d_gpu_dt_ptr(hf2d_gpu* h, void** dev_ptr);
 void* hf2d_gpu_stream(hf2d_gpu* h);   /* cudaStream_t the handle launches on */
+int  hf2d_gpu_set_stream(hf2d_gpu* h, void* cuda_stream);   /* launch on the caller's stream instead */
+int  hf2d_gpu_dt_export(hf2d_gpu* h, void* dev_double);     /* running dt minimum -> caller's device double */
+int  hf2d_gpu_dt_import(hf2d_gpu* h, const void* dev_double);
+unsigned long long hf2d_gpu_launch_count(hf2d_gpu* h);      /* kernels launched through this handle so far */
 
 #ifdef __cplusplus
 }

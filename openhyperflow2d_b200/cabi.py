@@ -62,7 +62,8 @@ _lib = None
 EXPORTS = ["hf2d_gpu_last_error", "hf2d_gpu_device_count", "hf2d_gpu_create", "hf2d_gpu_destroy", "hf2d_gpu_upload_aos",
            "hf2d_gpu_download_aos", "hf2d_gpu_step", "hf2d_gpu_run_cycle", "hf2d_gpu_field_ptr", "hf2d_gpu_active_cells",
            "hf2d_gpu_bytes_per_cell", "hf2d_gpu_halo_bytes", "hf2d_gpu_halo_pack", "hf2d_gpu_halo_unpack", "hf2d_gpu_step_begin",
-           "hf2d_gpu_step_stage1", "hf2d_gpu_step_stage2", "hf2d_gpu_step_end", "hf2d_gpu_dt_ptr", "hf2d_gpu_stream"]
+           "hf2d_gpu_step_stage1", "hf2d_gpu_step_stage2", "hf2d_gpu_step_end", "hf2d_gpu_dt_ptr", "hf2d_gpu_stream",
+           "hf2d_gpu_set_stream", "hf2d_gpu_dt_export", "hf2d_gpu_dt_import", "hf2d_gpu_launch_count"]
 
 
 def lib():
@@ -90,6 +91,11 @@ def lib():
         L.hf2d_gpu_dt_ptr.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
         L.hf2d_gpu_stream.argtypes = [C.c_void_p]
         L.hf2d_gpu_stream.restype = C.c_void_p
+        L.hf2d_gpu_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+        L.hf2d_gpu_dt_export.argtypes = [C.c_void_p, C.c_void_p]
+        L.hf2d_gpu_dt_import.argtypes = [C.c_void_p, C.c_void_p]
+        L.hf2d_gpu_launch_count.argtypes = [C.c_void_p]
+        L.hf2d_gpu_launch_count.restype = C.c_ulonglong
         _lib = L
     return _lib
 
@@ -194,3 +200,41 @@ class Solver:
         b = C.c_double()
         _ck(lib().hf2d_gpu_bytes_per_cell(self._h, C.byref(b)))
         return b.value
+
+    # --- split step / halo API (multi-GPU drivers) ---
+    def set_stream(self, cuda_stream: int):
+        _ck(lib().hf2d_gpu_set_stream(self._h, C.c_void_p(cuda_stream)))
+
+    def halo_bytes(self, phase: int) -> int:
+        return lib().hf2d_gpu_halo_bytes(self._h, phase)
+
+    def halo_pack(self, side: int, phase: int, dev_ptr: int):
+        _ck(lib().hf2d_gpu_halo_pack(self._h, side, phase, C.c_void_p(dev_ptr)))
+
+    def halo_unpack(self, side: int, phase: int, dev_ptr: int):
+        _ck(lib().hf2d_gpu_halo_unpack(self._h, side, phase, C.c_void_p(dev_ptr)))
+
+    def step_begin(self):
+        _ck(lib().hf2d_gpu_step_begin(self._h))
+
+    def step_stage1(self):
+        _ck(lib().hf2d_gpu_step_stage1(self._h))
+
+    def step_stage2(self):
+        _ck(lib().hf2d_gpu_step_stage2(self._h))
+
+    def step_end(self, want_report=False):
+        if want_report:
+            rep = StepReport()
+            _ck(lib().hf2d_gpu_step_end(self._h, C.byref(rep)))
+            return rep
+        _ck(lib().hf2d_gpu_step_end(self._h, None))
+
+    def dt_export(self, dev_ptr: int):
+        _ck(lib().hf2d_gpu_dt_export(self._h, C.c_void_p(dev_ptr)))
+
+    def dt_import(self, dev_ptr: int):
+        _ck(lib().hf2d_gpu_dt_import(self._h, C.c_void_p(dev_ptr)))
+
+    def launch_count(self) -> int:
+        return int(lib().hf2d_gpu_launch_count(self._h))

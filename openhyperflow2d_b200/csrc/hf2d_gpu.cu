@@ -26,6 +26,8 @@ struct hf2d_gpu {
     hf2d_cfg cfg;
     int device;
     cudaStream_t stream;
+    cudaStream_t stream0;           // the stream created with the handle
+    bool own_stream;
     cudaEvent_t ev0, ev1;
     Params P;                       // device pointers + configuration, passed by value to the kernels
     std::vector<void*> allocs;
@@ -74,6 +76,7 @@ extern "C" int hf2d_gpu_create(const hf2d_cfg* cfg, int device, hf2d_gpu** out) 
     h->d_nlist = h->d_wall_list = nullptr; h->n_nlist = h->n_wall = 0; h->n_active = 0;
     for (int t = 0; t < HF2D_NTABLES; t++) { h->cfg.tab[t].x = nullptr; h->cfg.tab[t].y = nullptr; }
     CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    h->stream0 = h->stream; h->own_stream = true;
     CK(cudaEventCreate(&h->ev0)); CK(cudaEventCreate(&h->ev1));
     std::vector<DevTable> tabs(HF2D_NTABLES);
     for (int t = 0; t < HF2D_NTABLES; t++) {
@@ -115,7 +118,7 @@ extern "C" int hf2d_gpu_destroy(hf2d_gpu* h) {
     if (h->d_stage) cudaFree(h->d_stage);
     if (h->h_st) cudaFreeHost(h->h_st);
     cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
-    cudaStreamDestroy(h->stream);
+    cudaStreamDestroy(h->stream0);
     delete h;
     return HF2D_OK;
 }
