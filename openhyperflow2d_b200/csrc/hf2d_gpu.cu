@@ -42,6 +42,8 @@ struct hf2d_gpu {
     int *d_nlist, *d_wall_list;
     int n_nlist, n_wall;
     std::vector<int> level_first, level_count;
+    bool chain_mode;                // Neumann dependencies are linear chains: one pass + chain walk instead of level launches
+    int n_chains; int *d_chain_start, *d_chain_src; ChainElem* d_chain_el;
     long long n_active;
     unsigned last_iter_cycle;       // last_iter of the reference (fixed during one cycle)
     uint64_t launches;

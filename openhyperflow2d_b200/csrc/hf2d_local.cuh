@@ -40,6 +40,8 @@ __device__ __forceinline__ void local_update(const Params& P, const StepState& s
     const bool act = node_active(ct);
     const bool fc = !act && is_set(ct, NT_FC) && !is_set(ct, CT_SOLID);
     L.active = act; L.fc = fc; L.filled = false;
+    // NT_FC nodes always run FillNode2D(1,0,...) (deeps2d_core.cpp:1331), active nodes follow TurbStartIter (:1240-1244)
+    const int is_init = fc ? 0 : st.is_init;
     const int ne = num_eq(tt);
     const int nk = (P.ns && (tt & (TCT_k_eps_Model | TCT_SA_Model))) ? NEQ : 7;  // planes that can matter here
     // ---- commit (active nodes only) ----
@@ -73,7 +75,7 @@ __device__ __forceinline__ void local_update(const Params& P, const StepState& s
             } else if (is_set(tt, TCT_k_eps_Model)) {
                 const double l = OMAX(P.l_min[m], OMIN(P.dy, P.dx)) * 0.41;
                 const double p34 = (P.tem == TEM_k_eps_RNG) ? P.pow_cmu_34[1] : P.pow_cmu_34[0];
-                if (st.is_init) {
+                if (is_init) {
                     const double TmpI = P.turb_I * sqrt(L.U * L.U + L.V * L.V + 1.e-30);
                     L.S[iK] = 1.5 * TmpI * TmpI * L.S[iRho];
                     L.S[iEps] = p34 * pow15(L.S[iK] / L.S[iRho]) / l;
@@ -85,7 +87,7 @@ __device__ __forceinline__ void local_update(const Params& P, const StepState& s
                 if (is_set(tt, TCT_eps_CONST)) L.S[iEps] = p34 * pow15(L.S[iK] / L.S[iRho]) / l;
                 if (is_set(tt, TCT_eps_Cmk2kXn_WALL)) L.S[iEps] = p34 * pow15(L.S[iK] / L.S[iRho]) / l;
             } else if (is_set(tt, TCT_SA_Model)) {
-                if (st.is_init) L.S[iNut] = L.mu / L.S[iRho] / 100.0;
+                if (is_init) L.S[iNut] = L.mu / L.S[iRho] / 100.0;
                 else if (is_set(ct, CT_WALL_NO_SLIP) || is_set(ct, CT_WALL_LAW) || is_set(tt, TCT_k_CONST)) L.S[iNut] = 0.;
                 else if (is_set(ct, NT_FC)) L.S[iNut] = L.mu / L.S[iRho] * P.turb_I;
             }

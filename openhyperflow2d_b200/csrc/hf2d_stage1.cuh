@@ -81,6 +81,27 @@ __global__ void k_neumann_level(Params P, const int* __restrict__ list, int firs
     }
 }
 
+// Chains: when an overwritten S[k] of a node depends on the overwritten S[k] of its left/down neighbour (e.g. the
+// eps equation along a whole d/dy=0 row, a side effect of the flag quirk at deeps2d_core.cpp:918-930) the values
+// form a first-order recurrence that must be evaluated in sweep order to stay bit-exact.  k_neumann_level has
+// already produced every link-free value; one thread per chain then walks its links, carrying the running value
+// in a register; the `other` operands do not depend on the carry, so their loads overlap.
+__global__ void k_neumann_chains(Params P, const int* __restrict__ chain_start, const int* __restrict__ chain_src,
+                                 const ChainElem* __restrict__ el, int n_chains) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n_chains) return;
+    const int e0 = chain_start[c], e1 = chain_start[c + 1];
+    const long long N = P.N;
+    double carry = P.S_in[(long long)el[e0].k * N + chain_src[c]];
+#pragma unroll 4
+    for (int e = e0; e < e1; e++) {
+        const ChainElem q = el[e];
+        const double o = q.other_spec ? P.spec[q.other].S0[q.k] : P.S_in[(long long)q.k * N + q.other];
+        carry = (carry * (double)q.wc + o * (double)q.wo) * (double)q.sc;
+        P.S_in[(long long)q.k * N + q.node] = carry;
+    }
+}
+
 // this-sweep value of dSdx[k] (dir 0) / dSdy[k] (dir 1) of node m, for soft-BC readers behind it in the sweep
 __device__ __forceinline__ double ds_new(const Params& P, long long m, int k, int dir) {
     const uint32_t ct = P.ct[m], tt = P.tt[m];

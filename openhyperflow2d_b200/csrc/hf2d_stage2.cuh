@@ -44,7 +44,7 @@ __device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v)
 __global__ void __launch_bounds__(S2_BX * S2_BY) k_stage2(Params P) {
     __shared__ double sh_d[2 * NEQ][S2_BX * S2_BY / 32];
     __shared__ unsigned long long sh_u[2 * NEQ + 2][S2_BX * S2_BY / 32];
-    const StepState st = *P.st;   // read-only snapshot (the accumulators are only touched through atomics)
+    StepState st = *P.st;         // snapshot (the accumulators are only touched through atomics)
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     const int i = P.i_lo + blockIdx.y * blockDim.y + threadIdx.y;
     const bool inb = (j < P.ny && i < P.i_hi);
@@ -61,6 +61,7 @@ __global__ void __launch_bounds__(S2_BX * S2_BY) k_stage2(Params P) {
     const bool act = inb && node_active(ct);
     const bool fc = inb && !act && is_set(ct, NT_FC) && !is_set(ct, CT_SOLID);
     if (act || fc) {
+        if (fc) { st.is_init = 0; st.is_mu_t = 1; }   // NT_FC nodes: FillNode2D(1,0,...) regardless of TurbStartIter (:1331)
         const int ne = num_eq(tt);
         const bool turb2 = P.ns && (is_set(tt, TCT_k_eps_Model) || is_set(tt, TCT_SA_Model));
         const bool hasturb = P.ns && (tt & (TCT_k_eps_Model | TCT_SA_Model));

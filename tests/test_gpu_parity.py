@@ -111,5 +111,7 @@ def test_run_cycle_roundtrip_and_errors():
     # upload -> download with zero steps leaves the image untouched
     J0 = np.array(c["state0"], copy=True)
     s.upload_aos(J0); s.download_aos(J0)
-    assert J0.tobytes() == c["state0"].tobytes()
+    for f in J0.dtype.names:      # (np.array(copy=True) does not copy the padding between members: compare by member)
+        a, b = J0[f], c["state0"][f]
+        assert ((a == b) | ((a != a) & (b != b))).all(), f
     s.close()
