@@ -66,6 +66,10 @@ typedef struct hf2d_cfg {
     int    dt_rule;             /* 0 = serial running minimum (deeps2d_core.cpp:803,1326; the oracle's rule),
                                    1 = per-step minimum (MPI build, :806-809,850)                           */
     int    rank, n_ranks;       /* X-slab index / count; 0,1 for a single GPU                               */
+    int    NOutStep;            /* the reference reads the residual norms only on steps with iter % NOutStep == 0
+                                   (SaveRMS / progress line, deeps2d_core.cpp:1602-1637) and after the last step of
+                                   a cycle (exit monitor, :1870-1880): hf2d_gpu_step() reduces them on exactly those
+                                   steps of a call.  0 or 1 = every step.                                       */
 } hf2d_cfg;
 
 /* Byte offsets of the members of the caller's FlowNode2D record (offsetof on the reference's own header).
@@ -121,6 +125,9 @@ int  hf2d_gpu_run_cycle(hf2d_gpu* h, void* J, const hf2d_node_layout* layout, in
  * "l_min","y_plus" (k = 0).  Returns the CURRENT device pointer of that plane (nx*ny doubles, x-major). */
 int  hf2d_gpu_field_ptr(hf2d_gpu* h, const char* name, int k, void** dev_ptr);
 int  hf2d_gpu_active_cells(hf2d_gpu* h, long long* n_active, long long* n_total);
+/* strip-sweep tiles of the current grid: `plain` tiles (unflagged interior nodes only) run the specialised kernels,
+ * `general` tiles the flag-decoding ones; tile = tile_cols columns x tile_rows rows */
+int  hf2d_gpu_tile_counts(hf2d_gpu* h, int* n_plain, int* n_general, int* tile_cols, int* tile_rows);
 /* algorithmic bytes per active cell per step of the current configuration */
 int  hf2d_gpu_bytes_per_cell(hf2d_gpu* h, double* bytes);
 

@@ -36,7 +36,7 @@ class Cfg(C.Structure):
         ("SigW", C.c_double), ("SigF", C.c_double), ("delta_bl", C.c_double), ("turb_intensity", C.c_double),
         ("isAdiabaticWall", C.c_int), ("isAlternateRMS", C.c_int), ("AddSrcStartIter", C.c_uint), ("last_iter", C.c_uint),
         ("MonitorIndex", C.c_int), ("ExitMonitorValue", C.c_double), ("K0", C.c_double), ("Rgas", C.c_double * 4),
-        ("tab", Table * NTAB), ("dt_rule", C.c_int), ("rank", C.c_int), ("n_ranks", C.c_int),
+        ("tab", Table * NTAB), ("dt_rule", C.c_int), ("rank", C.c_int), ("n_ranks", C.c_int), ("NOutStep", C.c_int),
     ]
 
 
@@ -61,7 +61,7 @@ class Hf2dError(RuntimeError):
 _lib = None
 EXPORTS = ["hf2d_gpu_last_error", "hf2d_gpu_device_count", "hf2d_gpu_create", "hf2d_gpu_destroy", "hf2d_gpu_upload_aos",
            "hf2d_gpu_download_aos", "hf2d_gpu_step", "hf2d_gpu_run_cycle", "hf2d_gpu_field_ptr", "hf2d_gpu_active_cells",
-           "hf2d_gpu_bytes_per_cell", "hf2d_gpu_halo_bytes", "hf2d_gpu_halo_pack", "hf2d_gpu_halo_unpack", "hf2d_gpu_step_begin",
+           "hf2d_gpu_bytes_per_cell", "hf2d_gpu_tile_counts", "hf2d_gpu_halo_bytes", "hf2d_gpu_halo_pack", "hf2d_gpu_halo_unpack", "hf2d_gpu_step_begin",
            "hf2d_gpu_step_stage1", "hf2d_gpu_step_stage2", "hf2d_gpu_step_end", "hf2d_gpu_dt_ptr", "hf2d_gpu_stream",
            "hf2d_gpu_set_stream", "hf2d_gpu_dt_export", "hf2d_gpu_dt_import", "hf2d_gpu_launch_count"]
 
@@ -80,6 +80,7 @@ def lib():
         L.hf2d_gpu_run_cycle.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(NodeLayout), C.c_int, C.c_int, C.POINTER(StepReport)]
         L.hf2d_gpu_field_ptr.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.POINTER(C.c_void_p)]
         L.hf2d_gpu_active_cells.argtypes = [C.c_void_p, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]
+        L.hf2d_gpu_tile_counts.argtypes = [C.c_void_p] + [C.POINTER(C.c_int)] * 4
         L.hf2d_gpu_bytes_per_cell.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
         L.hf2d_gpu_halo_bytes.argtypes = [C.c_void_p, C.c_int]
         L.hf2d_gpu_halo_bytes.restype = C.c_size_t
@@ -113,7 +114,7 @@ def make_layout(layout: dict) -> NodeLayout:
     return nl
 
 
-def make_cfg(cfg: dict, nx=None, ny=None, rank=0, n_ranks=1, dt_rule=0):
+def make_cfg(cfg: dict, nx=None, ny=None, rank=0, n_ranks=1, dt_rule=0, rms_every=None):
     c = Cfg()
     keep = []
     c.nx, c.ny = nx or cfg["MaxX"], ny or cfg["MaxY"]
@@ -138,6 +139,7 @@ def make_cfg(cfg: dict, nx=None, ny=None, rank=0, n_ranks=1, dt_rule=0):
         c.tab[i].x = C.cast(xa, C.POINTER(C.c_double))
         c.tab[i].y = C.cast(ya, C.POINTER(C.c_double))
     c.dt_rule, c.rank, c.n_ranks = dt_rule, rank, n_ranks
+    c.NOutStep = int(cfg.get("NOutStep", 1)) if rms_every is None else int(rms_every)
     return c, keep
 
 
@@ -195,6 +197,11 @@ class Solver:
         a, t = C.c_longlong(), C.c_longlong()
         _ck(lib().hf2d_gpu_active_cells(self._h, C.byref(a), C.byref(t)))
         return a.value, t.value
+
+    def tile_counts(self):
+        v = [C.c_int() for _ in range(4)]
+        _ck(lib().hf2d_gpu_tile_counts(self._h, *[C.byref(x) for x in v]))
+        return tuple(x.value for x in v)
 
     def bytes_per_cell(self) -> float:
         b = C.c_double()

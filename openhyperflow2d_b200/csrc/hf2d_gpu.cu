@@ -49,6 +49,11 @@ struct hf2d_gpu {
     uint64_t launches;
     void* d_stage; size_t stage_bytes;
     double bytes_per_cell;
+    // strip-sweep tiles (hf2d_stage2.cuh): TI columns x S2_WARPS strips of STRIP_ROWS rows
+    int TI, n_sb, n_tx;
+    int *d_tiles_plain, *d_tiles_gen; int n_plain, n_gen;
+    int plain_ttc;                  // TurbType word of the plain tiles (-1: no plain kernel for this grid)
+    int rms_every;                  // residual norms are reduced on steps with iter % rms_every == 0 and on the last step of a call
 };
 
 extern "C" const char* hf2d_gpu_last_error(void) { return g_err; }
@@ -108,6 +113,8 @@ extern "C" int hf2d_gpu_create(const hf2d_cfg* cfg, int device, hf2d_gpu** out) 
     P.pow_cmu_34[0] = pow(0.09, 3. / 4.); P.pow_cmu_34[1] = pow(0.0845, 3. / 4.);
     P.tab = h->d_tab; P.st = h->d_st;
     h->last_iter_cycle = cfg->last_iter;
+    h->rms_every = cfg->NOutStep;
+    h->TI = 16; h->n_sb = h->n_tx = 0; h->d_tiles_plain = h->d_tiles_gen = nullptr; h->n_plain = h->n_gen = 0; h->plain_ttc = -1;
     *out = h;
     return HF2D_OK;
 }
@@ -125,5 +132,6 @@ extern "C" int hf2d_gpu_destroy(hf2d_gpu* h) {
     return HF2D_OK;
 }
 
+static bool plain_ttc_supported(int ttc);
 #include "hf2d_io.inc"
 #include "hf2d_step.inc"

@@ -33,32 +33,28 @@ __device__ __forceinline__ bool eq_committed(uint32_t ct, uint32_t tt, int k, in
     return false;
 }
 
+// Kernel configuration: solver mode and flow type are compile-time; TTC >= 0 marks a "plain" instantiation whose
+// nodes are all unflagged interior nodes (CT == CT_NODE_IS_SET, TurbType == TTC, four neighbours present), so that
+// every flag test below constant-folds; TTC < 0 reads the flag words of each node.
+template <int NS, int AXI, int TTC> struct KCfg {
+    static constexpr int ns = NS, axi = AXI, ttc = TTC;
+    static constexpr bool plain = TTC >= 0;
+};
+
+// The part of local_update that follows the commit loop: L.S[] holds the committed S of node m.
 // FULL=false computes only what neighbours read (S[0], S[4..8] post-chemistry, U, V, Tg).
-template <bool FULL>
-__device__ __forceinline__ void local_update(const Params& P, const StepState& st, long long m, uint32_t ct, uint32_t tt, Local& L) {
-    const long long N = P.N;
+template <class KC, bool FULL>
+__device__ __forceinline__ void local_rest(const Params& P, const StepState& st, long long m, uint32_t ct, uint32_t tt, Local& L) {
     const bool act = node_active(ct);
     const bool fc = !act && is_set(ct, NT_FC) && !is_set(ct, CT_SOLID);
     L.active = act; L.fc = fc; L.filled = false;
     // NT_FC nodes always run FillNode2D(1,0,...) (deeps2d_core.cpp:1331), active nodes follow TurbStartIter (:1240-1244)
     const int is_init = fc ? 0 : st.is_init;
-    const int ne = num_eq(tt);
-    const int nk = (P.ns && (tt & (TCT_k_eps_Model | TCT_SA_Model))) ? NEQ : 7;  // planes that can matter here
-    // ---- commit (active nodes only) ----
-#pragma unroll
-    for (int k = 0; k < NEQ; k++) {
-        double s = 0.;
-        if (k < 7 || k < nk) {
-            s = P.S_in[(long long)k * N + m];
-            if (act && k < ne && eq_committed(ct, tt, k, P.ns)) s = P.SN[(long long)k * N + m];
-        }
-        L.S[k] = s;
-    }
     L.s7c = L.S[7]; L.s8c = L.S[8];
     L.Uo = P.U_in[m]; L.Vo = P.V_in[m]; L.Tgo = P.Tg_in[m];
     L.U = L.Uo; L.V = L.Vo; L.Tg = L.Tgo;
     L.CP = P.CP_in[m]; L.R = P.R_in[m];
-    L.mu = P.ns ? P.mu_in[m] : 0.;
+    L.mu = KC::ns ? P.mu_in[m] : 0.;
     const double kg_old = P.kg[m];
     L.kg = kg_old;
     if (FULL) { L.po = P.p[m]; L.p = L.po; }
@@ -69,7 +65,7 @@ __device__ __forceinline__ void local_update(const Params& P, const StepState& s
         L.kg = L.CP / (L.CP - L.R);
         if (is_set(ct, CT_U_CONST)) L.S[iRhoU] = L.U * L.S[iRho]; else L.U = L.S[iRhoU] / L.S[iRho];
         if (is_set(ct, CT_V_CONST)) L.S[iRhoV] = L.V * L.S[iRho]; else L.V = L.S[iRhoV] / L.S[iRho];
-        if (P.ns && (tt & TT_MASK) != 0) {
+        if (KC::ns && (tt & TT_MASK) != 0) {
             // the S-rewriting part of TurbModRANS2D (:753-779 k-eps, :856-862 SA)
             if (is_set(tt, TCT_Prandtl_Model)) {
             } else if (is_set(tt, TCT_k_eps_Model)) {

@@ -103,11 +103,12 @@ __global__ void k_neumann_chains(Params P, const int* __restrict__ chain_start, 
 }
 
 // this-sweep value of dSdx[k] (dir 0) / dSdy[k] (dir 1) of node m, for soft-BC readers behind it in the sweep
+template <class KC>
 __device__ __forceinline__ double ds_new(const Params& P, long long m, int k, int dir) {
     const uint32_t ct = P.ct[m], tt = P.tt[m];
     const double* oldp = dir ? P.dSy_in[k] : P.dSx_in[k];
     if (!node_active(ct) || k >= num_eq(tt)) return oldp[m];
-    const unsigned f = eq_flags(ct, tt, k, P.ns);
+    const unsigned f = eq_flags(ct, tt, k, KC::ns);
     if (!(f & 1)) return oldp[m];
     if (dir == 0) {
         if (!(f & 2)) return 0.;
@@ -124,67 +125,86 @@ __device__ __forceinline__ double ds_new(const Params& P, long long m, int k, in
     }
 }
 
-__global__ void __launch_bounds__(256) k_stage1(Params P) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    const int i = P.i_lo + blockIdx.y * blockDim.y + threadIdx.y;
-    if (j >= P.ny || i >= P.i_hi) return;
-    const long long ny = P.ny, N = P.N, n = (long long)i * ny + j;
-    const uint32_t ct = P.ct[n], tt = P.tt[n];
-    const bool act = node_active(ct);
-    const int ne = act ? num_eq(tt) : 0;
-    // tracked dS planes must be carried over for nodes / equations that are not advanced
-    if (P.need_dsx | P.need_dsy) {
-        for (int k = 0; k < NEQ; k++) {
-            const bool adv = act && k < ne && (eq_flags(ct, tt, k, P.ns) & 1);
-            if (!adv) {
-                if (P.need_dsx & (1u << k)) P.dSx_out[k][n] = P.dSx_in[k][n];
-                if (P.need_dsy & (1u << k)) P.dSy_out[k][n] = P.dSy_in[k][n];
-            }
-        }
-    }
-    if (!act) return;
-    const int n1 = (tt & TT_IDXL) ? 1 : 0, n2 = (tt & TT_IDXR) ? 1 : 0, n3 = (tt & TT_IDYU) ? 1 : 0, n4 = (tt & TT_IDYD) ? 1 : 0;
-    const long long nL = n - n1 * ny, nR = n + n2 * ny, nU = n + n3, nD = n - n4;
-    const double n_n = OMAX(n1 + n2, 1), m_m = OMAX(n3 + n4, 1);
-    const double n_n_1 = 1. / n_n, m_m_1 = 1. / m_m;
-    const uint32_t ttR = n2 ? P.tt[nR] : 0u, ttU = n3 ? P.tt[nU] : 0u;
+// Strip sweep (same tiles as Stage 2, hf2d_stage2.cuh): a warp owns STRIP_ROWS consecutive rows and walks TI columns.
+// KC::plain instantiations serve tiles whose nodes and whole neighbour ring are unflagged interior nodes: every
+// equation is advanced with plain central differences, no special-node look-ups.
+#define STRIP_ROWS 31
+#define S1_WARPS 4
+#define S1_THREADS (32 * S1_WARPS)
+
+template <class KC>
+__global__ void __launch_bounds__(S1_THREADS) k_stage1(Params P, const int* __restrict__ tiles, int n_sb, int TI) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int tile = tiles[blockIdx.x];
+    const int tx = tile / n_sb, sb = tile - tx * n_sb;
+    const int j = (sb * S1_WARPS + warp) * STRIP_ROWS + lane;
+    if (lane >= STRIP_ROWS || j >= P.ny) return;
+    const int i0 = P.i_lo + tx * TI, i1 = min(i0 + TI, P.i_hi);
+    const long long ny = P.ny, N = P.N;
     const double dt = P.st->dt;
     const double dtdx = dt / P.dx, dtdy = dt / P.dy;                  // :843-844
     const double dyy = P.dx / (P.dx + P.dy), dxx = P.dy / (P.dx + P.dy);   // :643-644
-    const SpecNode* sp = (tt & TT_SPEC) ? &P.spec[P.spec_idx[n]] : nullptr;
-    for (int k = 0; k < ne; k++) {
-        const unsigned f = eq_flags(ct, tt, k, P.ns);
-        if (!(f & 1)) continue;
-        const long long o = (long long)k * N;
-        const double beta = P.beta[o + n], _beta = 1. - beta;
-        const double sc = P.S_in[o + n];
-        const double sl = P.S_in[o + nL], sd = P.S_in[o + nD];
-        const double sr = n2 ? s_old(P, nR, ttR, k) : sc;
-        const double su = n3 ? s_old(P, nU, ttU, k) : sc;
-        double dXX, dYY;
-        if (f & 2) dXX = (P.A[o + nR] - P.A[o + nL]) * n_n_1; else dXX = 0.;
-        if (f & 4) dYY = (P.B[o + nU] - P.B[o + nD]) * m_m_1; else dYY = 0.;
-        if (P.need_dsx & (1u << k)) P.dSx_out[k][n] = dXX;
-        if (P.need_dsy & (1u << k)) P.dSy_out[k][n] = dYY;
-        if (f & 8) {    // :1008-1010  left: this sweep's value, right: last step's (own value if aliased)
-            const double dl = n1 ? ds_new(P, nL, k, 0) : dXX;
-            const double dr = n2 ? P.dSx_in[k][nR] : dXX;
-            dXX = (dl + dr) * 0.5;
+    for (int i = i0; i < i1; i++) {
+        const long long n = (long long)i * ny + j;
+        uint32_t ct, tt;
+        if (KC::plain) { ct = CT_NODE_IS_SET; tt = (uint32_t)KC::ttc | TT_IDXL | TT_IDXR | TT_IDYU | TT_IDYD; }
+        else { ct = P.ct[n]; tt = P.tt[n]; }
+        const bool act = node_active(ct);
+        const int ne = act ? num_eq(tt) : 0;
+        // tracked dS planes must be carried over for nodes / equations that are not advanced
+        if (!KC::plain && (P.need_dsx | P.need_dsy)) {
+            for (int k = 0; k < NEQ; k++) {
+                const bool adv = act && k < ne && (eq_flags(ct, tt, k, KC::ns) & 1);
+                if (!adv) {
+                    if (P.need_dsx & (1u << k)) P.dSx_out[k][n] = P.dSx_in[k][n];
+                    if (P.need_dsy & (1u << k)) P.dSy_out[k][n] = P.dSy_in[k][n];
+                }
+            }
         }
-        if (f & 16) {   // :1011-1013
-            const double du = n3 ? P.dSy_in[k][nU] : dYY;
-            const double dd = n4 ? ds_new(P, nD, k, 1) : dYY;
-            dYY = (du + dd) * 0.5;
+        if (!act) continue;
+        const int n1 = (tt & TT_IDXL) ? 1 : 0, n2 = (tt & TT_IDXR) ? 1 : 0, n3 = (tt & TT_IDYU) ? 1 : 0, n4 = (tt & TT_IDYD) ? 1 : 0;
+        const long long nL = n - n1 * ny, nR = n + n2 * ny, nU = n + n3, nD = n - n4;
+        const double n_n = OMAX(n1 + n2, 1), m_m = OMAX(n3 + n4, 1);
+        const double n_n_1 = 1. / n_n, m_m_1 = 1. / m_m;
+        uint32_t ttR = 0u, ttU = 0u;
+        if (!KC::plain) { ttR = n2 ? P.tt[nR] : 0u; ttU = n3 ? P.tt[nU] : 0u; }
+        const SpecNode* sp = (tt & TT_SPEC) ? &P.spec[P.spec_idx[n]] : nullptr;
+#pragma unroll
+        for (int k = 0; k < NEQ; k++) {
+            if (k >= ne) continue;
+            const unsigned f = eq_flags(ct, tt, k, KC::ns);
+            if (!(f & 1)) continue;
+            const long long o = (long long)k * N;
+            const double beta = P.beta[o + n], _beta = 1. - beta;
+            const double sc = P.S_in[o + n];
+            const double sl = P.S_in[o + nL], sd = P.S_in[o + nD];
+            const double sr = n2 ? s_old(P, nR, ttR, k) : sc;
+            const double su = n3 ? s_old(P, nU, ttU, k) : sc;
+            double dXX, dYY;
+            if (f & 2) dXX = (P.A[o + nR] - P.A[o + nL]) * n_n_1; else dXX = 0.;
+            if (f & 4) dYY = (P.B[o + nU] - P.B[o + nD]) * m_m_1; else dYY = 0.;
+            if (P.need_dsx & (1u << k)) P.dSx_out[k][n] = dXX;
+            if (P.need_dsy & (1u << k)) P.dSy_out[k][n] = dYY;
+            if (f & 8) {    // :1008-1010  left: this sweep's value, right: last step's (own value if aliased)
+                const double dl = n1 ? ds_new<KC>(P, nL, k, 0) : dXX;
+                const double dr = n2 ? P.dSx_in[k][nR] : dXX;
+                dXX = (dl + dr) * 0.5;
+            }
+            if (f & 16) {   // :1011-1013
+                const double du = n3 ? P.dSy_in[k][nU] : dYY;
+                const double dd = n4 ? ds_new<KC>(P, nD, k, 1) : dYY;
+                dYY = (du + dd) * 0.5;
+            }
+            double src = 0.;
+            if (k >= 7 || P.has_src) src = P.Src[o + n];
+            const double srcadd = sp ? sp->SrcAdd[k] : 0.;
+            double sn;
+            if (KC::axi) {
+                sn = sc * beta + _beta * (dxx * (sl + sr) + dyy * (su + sd)) * 0.5 - (dtdx * dXX + dtdy * (dYY + P.F[o + n] / (j + 1))) + src * dt + srcadd;
+            } else {
+                sn = sc * beta + _beta * (dxx * (sl + sr) + dyy * (su + sd)) * 0.5 - (dtdx * dXX + dtdy * dYY) + src * dt + srcadd;
+            }
+            P.SN[o + n] = sn;
         }
-        double src = 0.;
-        if (k >= 7 || P.has_src) src = P.Src[o + n];
-        const double srcadd = sp ? sp->SrcAdd[k] : 0.;
-        double sn;
-        if (P.axi) {
-            sn = sc * beta + _beta * (dxx * (sl + sr) + dyy * (su + sd)) * 0.5 - (dtdx * dXX + dtdy * (dYY + P.F[o + n] / (j + 1))) + src * dt + srcadd;
-        } else {
-            sn = sc * beta + _beta * (dxx * (sl + sr) + dyy * (su + sd)) * 0.5 - (dtdx * dXX + dtdy * dYY) + src * dt + srcadd;
-        }
-        P.SN[o + n] = sn;
     }
 }

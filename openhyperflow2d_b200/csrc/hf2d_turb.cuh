@@ -19,6 +19,7 @@ struct TurbOut {
 // the reference's pow(double,int) is __builtin_powi, expanded by g++ as x^3*x^3 with x^3=(x*x)*x (oracle/deeps2d_oracle.c)
 __device__ __forceinline__ double powi6(double x) { const double x3 = (x * x) * x; return x3 * x3; }
 
+template <class KC>
 __device__ __forceinline__ void turb_own(const Params& P, const StepState& st, long long m, uint32_t ct, uint32_t tt,
                                          const Local& L, const Grads& g, double yj, TurbOut& T) {
     const double rho = L.S[iRho];
@@ -36,15 +37,17 @@ __device__ __forceinline__ void turb_own(const Params& P, const StepState& st, l
     } else if (is_set(tt, TCT_k_eps_Model)) {
         double C1eps = 1.44, C2eps = 1.92, C_mu = 0.09, sig_k = 1.0, sig_eps = 1.3;
         const double f1 = 1.; double f2 = 1., f_mu = 1.;
-        double Rt, nu, G, L_k = 0, L_eps = 0, Mt = 0;
+        double Rt = 0, nu, G, L_k = 0, L_eps = 0, Mt = 0;
         const double Tmp1 = g.dUdy + g.dVdx;
         const double Tmp2 = rho * l;
         double Tmp3 = g.dUdx * g.dUdx + g.dVdy * g.dVdy;
-        if (P.axi) Tmp3 += L.U / yj;
+        if (KC::axi) Tmp3 += L.U / yj;
         if (T.mu_t == 0) T.mu_t = rho * l * l * OMAX(fabs(g.dUdy), fabs(g.dVdx));
         G = T.mu_t * (Tmp1 * Tmp1 + 2 * Tmp3);
         // Rt and the damping functions see S[k], S[eps] as committed, before this call's boundary rewrites
-        if (L.s8c != 0.0 && L.mu != 0.0) Rt = L.s7c * L.s7c / L.s8c / L.mu; else Rt = 0;
+        if (tem == TEM_k_eps_Chien || tem == TEM_k_eps_JL || tem == TEM_k_eps_LSY) {   // (the only variants that read Rt)
+            if (L.s8c != 0.0 && L.mu != 0.0) Rt = L.s7c * L.s7c / L.s8c / L.mu; else Rt = 0;
+        }
         if (tem == TEM_k_eps_Std) {
         } else if (tem == TEM_k_eps_Chien) {
             const double yp = P.y_plus[m];
@@ -82,8 +85,10 @@ __device__ __forceinline__ void turb_own(const Params& P, const StepState& st, l
                 }
             }
             // TurbulenceAxisymmAddOn (:242-252)
-            const double FT = (double)P.axi;
-            T.F7 = FT * (L.mu + T.mu_t) * g.dkdy; T.F8 = FT * (L.mu + T.mu_t / 1.3) * g.depsdy; T.wF7 = T.wF8 = true;
+            if (KC::axi) {
+                const double FT = (double)KC::axi;
+                T.F7 = FT * (L.mu + T.mu_t) * g.dkdy; T.F8 = FT * (L.mu + T.mu_t / 1.3) * g.depsdy; T.wF7 = T.wF8 = true;
+            }
         }
     } else if (is_set(tt, TCT_SA_Model)) {
         double fv1 = 1.0;
@@ -116,7 +121,7 @@ __device__ __forceinline__ void turb_own(const Params& P, const StepState& st, l
             T.wSrc7 = true;
         }
         // TurbulenceAxisymmAddOn
-        if (!is_init) { T.F7 = (double)P.axi * (L.mu / rho + S7) * g.dkdy; T.wF7 = true; }
+        if (!is_init) { if (KC::axi) { T.F7 = (double)KC::axi * (L.mu / rho + S7) * g.dkdy; T.wF7 = true; } }
         else { T.F7 = 0.; T.F8 = 0.; T.wF7 = T.wF8 = true; T.Src7 = 0.; T.Src8 = 0.; T.wSrc7 = T.wSrc8 = true; }
         if (is_mu_t) { T.mu_t = OMAX(0, (rho * S7 * fv1)); T.lam_t = T.mu_t * L.CP; T.w_lam_t = true; }
     } else if (is_set(tt, TCT_SST_Model)) {
