@@ -103,6 +103,7 @@ extern "C" int hf2d_gpu_create(const hf2d_cfg* cfg, int device, hf2d_gpu** out) 
     P.i_lo = (cfg->n_ranks > 1 && cfg->rank > 0) ? 1 : 0;
     P.i_hi = (cfg->n_ranks > 1 && cfg->rank < cfg->n_ranks - 1) ? cfg->nx - 1 : cfg->nx;
     P.dx = cfg->dx; P.dy = cfg->dy; P.CFL = cfg->CFL; P.beta0 = cfg->beta0; P.nrbc_beta0 = cfg->nrbc_beta0;
+    { const double dx_1 = 1.0 / cfg->dx, dy_1 = 1.0 / cfg->dy; P.dxn[0] = dx_1 / 1.0; P.dxn[1] = dx_1 / 2.0; P.dyn[0] = dy_1 / 1.0; P.dyn[1] = dy_1 / 2.0; }
     P.bFF = cfg->bFF; P.ns = cfg->problem_type == 1; P.axi = cfg->flow_type == 1;
     for (int q = 0; q < 4; q++) { P.Hu[q] = cfg->Hu[q]; P.Rgas[q] = cfg->Rgas[q]; }
     P.TurbStartIter = cfg->TurbStartIter; P.tem = cfg->TurbExtModel; P.isTurbulenceReset = cfg->isTurbulenceReset;

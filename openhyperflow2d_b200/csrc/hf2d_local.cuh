@@ -62,9 +62,9 @@ __device__ __forceinline__ void local_rest(const Params& P, const StepState& st,
     // ---- FillNode2D, local part (hyper_flow_node.hpp:382-492) ----
     if (!(L.S[iRho] == 0) && !(kg_old < 1)) {
         L.filled = true;
-        L.kg = L.CP / (L.CP - L.R);
-        if (is_set(ct, CT_U_CONST)) L.S[iRhoU] = L.U * L.S[iRho]; else L.U = L.S[iRhoU] / L.S[iRho];
-        if (is_set(ct, CT_V_CONST)) L.S[iRhoV] = L.V * L.S[iRho]; else L.V = L.S[iRhoV] / L.S[iRho];
+        L.kg = ddiv(L.CP, L.CP - L.R);
+        if (is_set(ct, CT_U_CONST)) L.S[iRhoU] = L.U * L.S[iRho]; else L.U = ddiv(L.S[iRhoU], L.S[iRho]);
+        if (is_set(ct, CT_V_CONST)) L.S[iRhoV] = L.V * L.S[iRho]; else L.V = ddiv(L.S[iRhoV], L.S[iRho]);
         if (KC::ns && (tt & TT_MASK) != 0) {
             // the S-rewriting part of TurbModRANS2D (:753-779 k-eps, :856-862 SA)
             if (is_set(tt, TCT_Prandtl_Model)) {
@@ -97,8 +97,8 @@ __device__ __forceinline__ void local_rest(const Params& P, const StepState& st,
             Tmp1 = sqrt(L.U * L.U + L.V * L.V + 1.e-30);
             L.S[iRhoU] = Tmp1 * sp.BGX;
             L.S[iRhoV] = Tmp1 * sp.BGY;
-            L.U = L.S[iRhoU] / L.S[iRho];
-            L.V = L.S[iRhoV] / L.S[iRho];
+            L.U = ddiv(L.S[iRhoU], L.S[iRho]);
+            L.V = ddiv(L.S[iRhoV], L.S[iRho]);
         } else if (is_set(ct, CT_WALL_NO_SLIP)) {
             const SpecNode& sp = P.spec[P.spec_idx[m]];
             if (FULL) { L.Upre = L.S[iRhoU] / L.S[iRho]; L.Vpre = L.S[iRhoV] / L.S[iRho]; }
@@ -107,22 +107,22 @@ __device__ __forceinline__ void local_rest(const Params& P, const StepState& st,
             L.S[iRhoV] = L.V * L.S[iRho];
         }
         const double pp = (L.kg - 1.) * (L.S[iRhoE] - L.S[iRho] * (L.U * L.U + L.V * L.V) * 0.5 - Tmp3);
-        L.Tg = pp / L.R / L.S[iRho];
+        L.Tg = ddiv(ddiv(pp, L.R), L.S[iRho]);
         if (FULL) L.p = pp;
     }
     // ---- species part of CalcChemicalReactions (deeps2d_core.cpp:4702-4728, 4748-4777); active nodes only ----
     L.y4 = L.S[4]; L.y5 = L.S[5]; L.y6 = L.S[6];
     if (act) {
-        double Yfu = L.S[iYfu] / L.S[0], Yox = L.S[iYox] / L.S[0], Ycp = L.S[iYcp] / L.S[0];
+        double Yfu = ddiv(L.S[iYfu], L.S[0]), Yox = ddiv(L.S[iYox], L.S[0]), Ycp = ddiv(L.S[iYcp], L.S[0]);
         double Yair = 1. - (Yfu + Yox + Ycp);
         const bool yconst = is_set(ct, CT_Y_CONST);
         if (!yconst) {
-            double Y0 = 1. / (Yfu + Yox + Ycp + Yair);
+            double Y0 = ddiv(1., Yfu + Yox + Ycp + Yair);
             Yfu = Yfu * Y0; Yox = Yox * Y0; Ycp = Ycp * Y0;
             const double Tf = P.tf_uniform ? P.Tf0 : P.Tf[m];
             if (L.Tg > Tf) {
                 if (Yox > Yfu * P.K0) { Yox = Yox - Yfu * P.K0; Yfu = 0.; Ycp = 1. - Yox - Yair; }
-                else { Yfu = Yfu - Yox / P.K0; Yox = 0.; Ycp = 1. - Yfu - Yair; }
+                else { Yfu = Yfu - ddiv(Yox, P.K0); Yox = 0.; Ycp = 1. - Yfu - Yair; }
             }
         }
         if (FULL) { L.Yfu = Yfu; L.Yox = Yox; L.Ycp = Ycp; L.Yair = Yair; }
@@ -130,7 +130,7 @@ __device__ __forceinline__ void local_rest(const Params& P, const StepState& st,
         if (Ycp < 1.e-8) Ycp = 0.;
         if (Yox < 1.e-8) Yox = 0.;
         if (Yfu < 1.e-8) Yfu = 0.;
-        const double Y0 = 1. / (Yfu + Yox + Ycp + Yair);
+        const double Y0 = ddiv(1., Yfu + Yox + Ycp + Yair);
         Yfu = Yfu * Y0; Yox = Yox * Y0; Ycp = Ycp * Y0; Yair = Yair * Y0;
         if (FULL) { L.Y[0] = Yfu; L.Y[1] = Yox; L.Y[2] = Ycp; L.Y[3] = Yair; }
         if (!yconst) { L.y4 = fabs(Yfu * L.S[0]); L.y5 = fabs(Yox * L.S[0]); L.y6 = fabs(Ycp * L.S[0]); }

@@ -133,17 +133,19 @@ __device__ __forceinline__ double ds_new(const Params& P, long long m, int k, in
 #define S1_THREADS (32 * S1_WARPS)
 
 template <class KC>
-__global__ void __launch_bounds__(S1_THREADS) k_stage1(Params P, const int* __restrict__ tiles, int n_sb, int TI) {
+__global__ void __launch_bounds__(S1_THREADS) k_stage1(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int tile = tiles[blockIdx.x];
+    const int t_idx = blockIdx.x * S1_WARPS + warp;
+    if (t_idx >= n_tiles) return;
+    const int tile = tiles[t_idx];
     const int tx = tile / n_sb, sb = tile - tx * n_sb;
-    const int j = (sb * S1_WARPS + warp) * STRIP_ROWS + lane;
+    const int j = sb * STRIP_ROWS + lane;
     if (lane >= STRIP_ROWS || j >= P.ny) return;
     const int i0 = P.i_lo + tx * TI, i1 = min(i0 + TI, P.i_hi);
     const long long ny = P.ny, N = P.N;
     const double dt = P.st->dt;
-    const double dtdx = dt / P.dx, dtdy = dt / P.dy;                  // :843-844
-    const double dyy = P.dx / (P.dx + P.dy), dxx = P.dy / (P.dx + P.dy);   // :643-644
+    const double dtdx = ddiv(dt, P.dx), dtdy = ddiv(dt, P.dy);                  // :843-844
+    const double dyy = ddiv(P.dx, P.dx + P.dy), dxx = ddiv(P.dy, P.dx + P.dy);   // :643-644
     for (int i = i0; i < i1; i++) {
         const long long n = (long long)i * ny + j;
         uint32_t ct, tt;
@@ -164,8 +166,7 @@ __global__ void __launch_bounds__(S1_THREADS) k_stage1(Params P, const int* __re
         if (!act) continue;
         const int n1 = (tt & TT_IDXL) ? 1 : 0, n2 = (tt & TT_IDXR) ? 1 : 0, n3 = (tt & TT_IDYU) ? 1 : 0, n4 = (tt & TT_IDYD) ? 1 : 0;
         const long long nL = n - n1 * ny, nR = n + n2 * ny, nU = n + n3, nD = n - n4;
-        const double n_n = OMAX(n1 + n2, 1), m_m = OMAX(n3 + n4, 1);
-        const double n_n_1 = 1. / n_n, m_m_1 = 1. / m_m;
+        const double n_n_1 = (n1 + n2 == 2) ? 0.5 : 1., m_m_1 = (n3 + n4 == 2) ? 0.5 : 1.;   // 1/max(n1+n2,1), 1/max(n3+n4,1)
         uint32_t ttR = 0u, ttU = 0u;
         if (!KC::plain) { ttR = n2 ? P.tt[nR] : 0u; ttU = n3 ? P.tt[nU] : 0u; }
         const SpecNode* sp = (tt & TT_SPEC) ? &P.spec[P.spec_idx[n]] : nullptr;
@@ -200,7 +201,7 @@ __global__ void __launch_bounds__(S1_THREADS) k_stage1(Params P, const int* __re
             const double srcadd = sp ? sp->SrcAdd[k] : 0.;
             double sn;
             if (KC::axi) {
-                sn = sc * beta + _beta * (dxx * (sl + sr) + dyy * (su + sd)) * 0.5 - (dtdx * dXX + dtdy * (dYY + P.F[o + n] / (j + 1))) + src * dt + srcadd;
+                sn = sc * beta + _beta * (dxx * (sl + sr) + dyy * (su + sd)) * 0.5 - (dtdx * dXX + dtdy * (dYY + ddiv(P.F[o + n], (double)(j + 1)))) + src * dt + srcadd;
             } else {
                 sn = sc * beta + _beta * (dxx * (sl + sr) + dyy * (su + sd)) * 0.5 - (dtdx * dXX + dtdy * dYY) + src * dt + srcadd;
             }

@@ -46,18 +46,20 @@ __device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v)
 #define S2_THREADS (32 * S2_WARPS)
 // STRIP_ROWS (31, hf2d_stage1.cuh): rows a warp owns; lane 0 is the halo row below them
 
-// tile t of the list covers columns [i_lo + tx*TI, +TI) x strips [sb*S2_WARPS, +S2_WARPS), t = tx * n_sb + sb
+// tile t covers columns [i_lo + tx*TI, +TI) x rows [sb*STRIP_ROWS, +STRIP_ROWS), t = tx * n_sb + sb; one warp per tile,
+// S2_WARPS consecutive entries of the tile list per block
 template <class KC>
 __global__ void __launch_bounds__(S2_THREADS, KC::plain ? 4 : 3)
-k_stage2(Params P, const int* __restrict__ tiles, int n_sb, int TI, int want_rms) {
+k_stage2(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI, int want_rms) {
     __shared__ double sh_acc[S2_WARPS][2 * NEQ];               // RMS, sumDiv partial sums of the warp (want_rms steps)
     __shared__ unsigned long long sh_u[S2_WARPS][2 * NEQ + 2]; // counts, max DD, dt-min, first error
     StepState st = *P.st;         // snapshot (the accumulators are only touched through atomics)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int tile = tiles[blockIdx.x];
+    const int t_idx = blockIdx.x * S2_WARPS + warp;
+    const int tile = t_idx < n_tiles ? tiles[t_idx] : 0;
     const int tx = tile / n_sb, sb = tile - tx * n_sb;
-    const int j = (sb * S2_WARPS + warp) * STRIP_ROWS + lane - 1;
-    const int i0 = P.i_lo + tx * TI, i1 = min(i0 + TI, P.i_hi);
+    const int j = sb * STRIP_ROWS + lane - 1;
+    const int i0 = P.i_lo + tx * TI, i1 = t_idx < n_tiles ? min(i0 + TI, P.i_hi) : i0;
     const bool valid_j = j >= 0 && j < P.ny;
     const bool owner_j = lane >= 1 && j < P.ny;
     const long long ny = P.ny, N = P.N;
@@ -106,19 +108,19 @@ k_stage2(Params P, const int* __restrict__ tiles, int n_sb, int TI, int want_rms
                         const double Tmp = s;
                         const double absDD = sn - s;
                         double DD, sqrt_RES = 0;
-                        if (fabs(Tmp) > 1.e-15) { DD = fabs(absDD / Tmp); if (P.bFF >= 4) sqrt_RES = sqrt(DD); } else { DD = 1.0; }
+                        if (fabs(Tmp) > 1.e-15) { DD = fabs(ddiv(absDD, Tmp)); if (P.bFF >= 4) sqrt_RES = dsqrt(DD); } else { DD = 1.0; }
                         double beta_min = OMIN(P.beta0, st.beta_scn);
                         if (is_set(ct, CT_NONREFLECTED)) beta_min = P.nrbc_beta0;
                         double* bp = &P.beta[o];
                         const double bb = beta_min * beta_min;
                         double bnew;
                         switch (P.bFF) {
-                        case 0: bnew = OMIN(beta_min, bb / (beta_min + DD)); break;
-                        case 1: bnew = OMIN((beta_min + *bp) * 0.5, bb / (beta_min + DD)); break;
-                        case 2: bnew = OMIN(beta_min, bb / (beta_min + DD * DD)); break;
-                        case 3: bnew = OMIN((beta_min + *bp) * 0.5, bb / (beta_min + DD * DD)); break;
-                        case 4: bnew = OMIN(beta_min, bb / (beta_min + sqrt_RES)); break;
-                        case 5: bnew = OMIN((beta_min + *bp) * 0.5, bb / (beta_min + sqrt_RES)); break;
+                        case 0: bnew = OMIN(beta_min, ddiv(bb, beta_min + DD)); break;
+                        case 1: bnew = OMIN((beta_min + *bp) * 0.5, ddiv(bb, beta_min + DD)); break;
+                        case 2: bnew = OMIN(beta_min, ddiv(bb, beta_min + DD * DD)); break;
+                        case 3: bnew = OMIN((beta_min + *bp) * 0.5, ddiv(bb, beta_min + DD * DD)); break;
+                        case 4: bnew = OMIN(beta_min, ddiv(bb, beta_min + sqrt_RES)); break;
+                        case 5: bnew = OMIN((beta_min + *bp) * 0.5, ddiv(bb, beta_min + sqrt_RES)); break;
                         default: bnew = *bp; break;
                         }
                         *bp = bnew;
@@ -169,8 +171,7 @@ k_stage2(Params P, const int* __restrict__ tiles, int n_sb, int TI, int want_rms
                     if (n1) nL = carry; else nL = own;
                     if (!n4) nD = own;
                     const double n_n = OMAX(n1 + n2, 1), m_m = OMAX(n3 + n4, 1);
-                    const double dx_1 = 1.0 / P.dx, dy_1 = 1.0 / P.dy;
-                    const double dxn = dx_1 / n_n, dym = dy_1 / m_m;
+                    const double dxn = (n1 + n2 == 2) ? P.dxn[1] : P.dxn[0], dym = (n3 + n4 == 2) ? P.dyn[1] : P.dyn[0];   // dx_1/n_n, dy_1/m_m (:1169)
                     double aR = nR.rho, aL = nL.rho, aU = nU.rho, aD = nD.rho;
                     const bool gx = !is_set(ct, CT_dYdx_NULL), gy = !is_set(ct, CT_dYdy_NULL);
                     // droYdx/droYdy keep their stored value when the species Neumann flag is set; nothing reads the
@@ -192,19 +193,19 @@ k_stage2(Params P, const int* __restrict__ tiles, int n_sb, int TI, int want_rms
                         g.dUdx = (nR.U * n1 - nL.U * n2) * dxn; g.dVdx = (nR.V * n1 - nL.V * n2) * dxn;
                         g.dUdy = (nU.U * n3 - nD.U * n4) * dym; g.dVdy = (nU.V * n3 - nD.V * n4) * dym;
                         if (is_set(tt, TCT_k_eps_Model)) {
-                            g.dkdx = (nR.s7 * n1 - nL.s7 * n2) * dxn / L.S[iRho]; g.depsdx = (nR.s8 * n1 - nL.s8 * n2) * dxn / L.S[iRho];
-                            g.dkdy = (nU.s7 * n3 - nD.s7 * n4) * dym / L.S[iRho]; g.depsdy = (nU.s8 * n3 - nD.s8 * n4) * dym / L.S[iRho];
+                            g.dkdx = ddiv((nR.s7 * n1 - nL.s7 * n2) * dxn, L.S[iRho]); g.depsdx = ddiv((nR.s8 * n1 - nL.s8 * n2) * dxn, L.S[iRho]);
+                            g.dkdy = ddiv((nU.s7 * n3 - nD.s7 * n4) * dym, L.S[iRho]); g.depsdy = ddiv((nU.s8 * n3 - nD.s8 * n4) * dym, L.S[iRho]);
                         } else if (is_set(tt, TCT_SA_Model)) {
-                            g.dkdx = (nR.s7 * n1 - nL.s7 * n2) * dxn / L.S[iRho]; g.dkdy = (nU.s7 * n3 - nD.s7 * n4) * dym / L.S[iRho];
+                            g.dkdx = ddiv((nR.s7 * n1 - nL.s7 * n2) * dxn, L.S[iRho]); g.dkdy = ddiv((nU.s7 * n3 - nD.s7 * n4) * dym, L.S[iRho]);
                         }
                     } else {
                         g.dUdx = (nR.U - nL.U) * dxn; g.dVdx = (nR.V - nL.V) * dxn;
                         g.dUdy = (nU.U - nD.U) * dym; g.dVdy = (nU.V - nD.V) * dym;
                         if (is_set(tt, TCT_k_eps_Model)) {
-                            g.dkdx = (nR.s7 - nL.s7) * dxn / L.S[iRho]; g.depsdx = (nR.s8 - nL.s8) * dxn / L.S[iRho];
-                            g.dkdy = (nU.s7 - nD.s7) * dym / L.S[iRho]; g.depsdy = (nU.s8 - nD.s8) * dym / L.S[iRho];
+                            g.dkdx = ddiv((nR.s7 - nL.s7) * dxn, L.S[iRho]); g.depsdx = ddiv((nR.s8 - nL.s8) * dxn, L.S[iRho]);
+                            g.dkdy = ddiv((nU.s7 - nD.s7) * dym, L.S[iRho]); g.depsdy = ddiv((nU.s8 - nD.s8) * dym, L.S[iRho]);
                         } else if (is_set(tt, TCT_SA_Model)) {
-                            g.dkdx = (nR.s7 - nL.s7) * dxn / L.S[iRho]; g.dkdy = (nU.s7 - nD.s7) * dym / L.S[iRho];
+                            g.dkdx = ddiv((nR.s7 - nL.s7) * dxn, L.S[iRho]); g.dkdy = ddiv((nU.s7 - nD.s7) * dym, L.S[iRho]);
                         }
                     }
                     g.dTdx = (nR.Tg - nL.Tg) * dxn; g.dTdy = (nU.Tg - nD.Tg) * dym;

@@ -79,7 +79,7 @@ def make_cfg(nx, ny, dx, dy, *, problem=1, flow_type=0, tem=4, turb_start=1, tur
     }
 
 
-def three_cylinders(nx, ny, *, layout=None, model="keps", mach=6.0, p_inf=5000.0, T_inf=220.0, Ts0=300.0, dx=2.5e-4, i0=0, nx_total=None):
+def three_cylinders(nx, ny, *, layout=None, model="keps", mach=6.0, p_inf=5000.0, T_inf=220.0, Ts0=300.0, dx=2.5e-4, i0=0, nx_total=None, bl_cells=24):
     """AoS image (nx, ny) of columns [i0, i0+nx) of an nx_total x ny domain with three solid cylinders in a Mach-6 stream.
 
     Returns (J, cfg, layout).  model: "keps" (9 equations), "sa" (8), "laminar" or "euler" (7)."""
@@ -133,7 +133,14 @@ def three_cylinders(nx, ny, *, layout=None, model="keps", mach=6.0, p_inf=5000.0
     kg = CP / (CP - R)
     rho = p_inf / (R * T_inf)
     U0 = mach * np.sqrt(kg * R * T_inf)
-    U = np.where(wall | solid, 0.0, U0) * np.ones((nx, ny))
+    # boundary-layer start profile around the bodies (the reference's SetInitBoundaryLayer, deeps2d_core.cpp:2243, does
+    # the same job for its decks): without it the impulsively started stream one cell off a no-slip wall drives k < 0
+    # within two steps.  U ramps from 0 at the surface to U0 over `bl_cells` cells.
+    dsurf = np.full((nx, ny), max(Lx, Ly))
+    for cx, cy in centres:
+        dsurf = np.minimum(dsurf, np.sqrt((X - cx) ** 2 + (Y - cy) ** 2) - r)
+    ramp = np.clip(dsurf / (bl_cells * dx), 0.0, 1.0)
+    U = np.where(wall | solid, 0.0, U0 * np.sin(0.5 * np.pi * ramp) ** 2) * np.ones((nx, ny))
     J["U"], J["V"] = U, 0.0
     J["p"] = p_inf
     J["Tg"] = np.where(solid, Ts0, T_inf)

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Join an ncu SASS source page with nvdisasm line info: executed warp instructions and stall samples per source line.
 
-usage: tools/ncu_by_line.py <report.ncu-rep> <kernel-name> [<mangled-substring>] [top]
+usage: tools/ncu_by_line.py <report.ncu-rep> <function-name>[@<substring of the demangled name>] [<mangled-substring>] [top]
 Needs ncu, cuobjdump and nvdisasm (all present in the build container; no GPU needed)."""
 import collections
 import csv
@@ -19,10 +19,12 @@ top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 so = os.path.join(ROOT, "openhyperflow2d_b200", "libhf2d_gpu.so")
 
-out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", kname], capture_output=True, text=True).stdout
+fn, _, sub = kname.partition("@")
+out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", "regex:" + fn], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
-# several launches of the same kernel may follow each other: take the first block
-hdr_i = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
+# several launches may follow each other: take the first block whose demangled name holds `sub`
+k_i = next(i for i, r in enumerate(rows) if r and r[0] == "Kernel Name" and sub in r[1])
+hdr_i = next(i for i, r in enumerate(rows) if i > k_i and r and r[0] == "Address")
 hdr = rows[hdr_i]
 body = []
 for r in rows[hdr_i + 1:]:
