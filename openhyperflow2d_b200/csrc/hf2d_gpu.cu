@@ -27,6 +27,8 @@ struct hf2d_gpu {
     int device;
     cudaStream_t stream;
     cudaStream_t stream0;           // the stream created with the handle
+    cudaStream_t stream_b;          // side stream: the general (boundary) tiles run beside the plain ones
+    cudaEvent_t ev_fork, ev_join;
     bool own_stream;
     cudaEvent_t ev0, ev1;
     Params P;                       // device pointers + configuration, passed by value to the kernels
@@ -85,6 +87,8 @@ extern "C" int hf2d_gpu_create(const hf2d_cfg* cfg, int device, hf2d_gpu** out) 
     CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     h->stream0 = h->stream; h->own_stream = true;
     CK(cudaEventCreate(&h->ev0)); CK(cudaEventCreate(&h->ev1));
+    CK(cudaStreamCreateWithFlags(&h->stream_b, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
     std::vector<DevTable> tabs(HF2D_NTABLES);
     for (int t = 0; t < HF2D_NTABLES; t++) {
         memset(&tabs[t], 0, sizeof(DevTable));
@@ -128,7 +132,7 @@ extern "C" int hf2d_gpu_destroy(hf2d_gpu* h) {
     if (h->d_stage) cudaFree(h->d_stage);
     if (h->h_st) cudaFreeHost(h->h_st);
     cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
-    cudaStreamDestroy(h->stream0);
+    cudaStreamDestroy(h->stream0); cudaStreamDestroy(h->stream_b); cudaEventDestroy(h->ev_fork); cudaEventDestroy(h->ev_join);
     delete h;
     return HF2D_OK;
 }

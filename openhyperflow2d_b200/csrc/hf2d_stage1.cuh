@@ -84,21 +84,41 @@ __global__ void k_neumann_level(Params P, const int* __restrict__ list, int firs
 // Chains: when an overwritten S[k] of a node depends on the overwritten S[k] of its left/down neighbour (e.g. the
 // eps equation along a whole d/dy=0 row, a side effect of the flag quirk at deeps2d_core.cpp:918-930) the values
 // form a first-order recurrence that must be evaluated in sweep order to stay bit-exact.  k_neumann_level has
-// already produced every link-free value; one thread per chain then walks its links, carrying the running value
+// already produced every link-free value; one warp per chain then walks its links, carrying the running value
 // in a register; the `other` operands do not depend on the carry, so their loads overlap.
-__global__ void k_neumann_chains(Params P, const int* __restrict__ chain_start, const int* __restrict__ chain_src,
-                                 const ChainElem* __restrict__ el, int n_chains) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+// One WARP per chain: the links are fetched 32 at a time (each lane loads one link record and its `other` operand, so
+// the two dependent global loads are paid once per 32 links instead of once per link), then the recurrence is replayed
+// in order with warp broadcasts; every lane carries the running value, lane t keeps the result of link t.
+__global__ void __launch_bounds__(32) k_neumann_chains(Params P, const int* __restrict__ chain_start, const int* __restrict__ chain_src,
+                                                       const ChainElem* __restrict__ el, int n_chains) {
+    const int c = blockIdx.x, lane = threadIdx.x;
     if (c >= n_chains) return;
     const int e0 = chain_start[c], e1 = chain_start[c + 1];
     const long long N = P.N;
     double carry = P.S_in[(long long)el[e0].k * N + chain_src[c]];
-#pragma unroll 4
-    for (int e = e0; e < e1; e++) {
-        const ChainElem q = el[e];
-        const double o = q.other_spec ? P.spec[q.other].S0[q.k] : P.S_in[(long long)q.k * N + q.other];
-        carry = (carry * (double)q.wc + o * (double)q.wo) * (double)q.sc;
-        P.S_in[(long long)q.k * N + q.node] = carry;
+    // software pipeline: operands of the next 32 links are loaded while the current 32 are replayed
+    ChainElem q; double t = 0.; q.node = 0; q.k = 0; q.wc = q.wo = q.sc = 0.f; q.other = 0; q.other_spec = 0;
+    auto fetch = [&](int e, ChainElem& qq, double& tt) {
+        if (e < e1) {
+            qq = el[e];
+            const double o = qq.other_spec ? P.spec[qq.other].S0[qq.k] : P.S_in[(long long)qq.k * N + qq.other];
+            tt = o * (double)qq.wo;
+        }
+    };
+    fetch(e0 + lane, q, t);
+    for (int eb = e0; eb < e1; eb += 32) {
+        ChainElem qn = q; double tn = 0.;
+        fetch(eb + 32 + lane, qn, tn);
+        const int cnt = min(32, e1 - eb);
+        double mine = 0.;
+        for (int s = 0; s < cnt; s++) {
+            const double ts = __shfl_sync(0xffffffffu, t, s);
+            const float wc = __shfl_sync(0xffffffffu, q.wc, s), sc = __shfl_sync(0xffffffffu, q.sc, s);
+            carry = (carry * (double)wc + ts) * (double)sc;
+            if (s == lane) mine = carry;
+        }
+        if (lane < cnt) P.S_in[(long long)q.k * N + q.node] = mine;
+        q = qn; t = tn;
     }
 }
 

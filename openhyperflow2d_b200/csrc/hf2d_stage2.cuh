@@ -113,17 +113,11 @@ k_stage2(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI,
                         if (is_set(ct, CT_NONREFLECTED)) beta_min = P.nrbc_beta0;
                         double* bp = &P.beta[o];
                         const double bb = beta_min * beta_min;
-                        double bnew;
-                        switch (P.bFF) {
-                        case 0: bnew = OMIN(beta_min, ddiv(bb, beta_min + DD)); break;
-                        case 1: bnew = OMIN((beta_min + *bp) * 0.5, ddiv(bb, beta_min + DD)); break;
-                        case 2: bnew = OMIN(beta_min, ddiv(bb, beta_min + DD * DD)); break;
-                        case 3: bnew = OMIN((beta_min + *bp) * 0.5, ddiv(bb, beta_min + DD * DD)); break;
-                        case 4: bnew = OMIN(beta_min, ddiv(bb, beta_min + sqrt_RES)); break;
-                        case 5: bnew = OMIN((beta_min + *bp) * 0.5, ddiv(bb, beta_min + sqrt_RES)); break;
-                        default: bnew = *bp; break;
-                        }
-                        *bp = bnew;
+                        // the six blending-factor functions (deeps2d_core.cpp:1104-1121): min(cap, bb / (beta_min + x))
+                        const double xx = (P.bFF >= 4) ? sqrt_RES : (P.bFF >= 2) ? DD * DD : DD;
+                        const double cap = (P.bFF & 1) ? (beta_min + *bp) * 0.5 : beta_min;
+                        const double quo = ddiv(bb, beta_min + xx);
+                        *bp = OMIN(cap, quo);
                         if (P.isAlternateRMS) { c_div = Tmp * Tmp; c_rms = absDD; } else { c_rms = DD * DD; }
                         c_cnt = 1u; c_dd = d2bits(DD);
                     }

@@ -124,6 +124,9 @@ def test_plain_tiles_match_oracle(model, nsteps):
     import oracle_py as O
     from openhyperflow2d_b200 import cabi, gridgen
     J, cfg, lay = gridgen.three_cylinders(176, 420, model=model)
+    # isAlternateRMS = 1 sums SIGNED residuals (deeps2d_core.cpp:1138-1143): on this symmetric flow they nearly cancel
+    # and a reordered summation has no relative error bound; the sum-of-squares norm is well conditioned
+    cfg["isAlternateRMS"] = 0
     nodes = O.nodes_from_ref(J)
     rc, dt_min, orep, tp = O.run_cycle(nodes, cfg, 0, nsteps, cfg["dt"])
     assert rc == 0
