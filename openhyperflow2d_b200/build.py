@@ -10,7 +10,7 @@ import subprocess
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-SO = os.path.join(HERE, "libhf2d_gpu.so")
+SO = os.path.join(HERE, os.environ.get("HF2D_SO_NAME", "libhf2d_gpu.so"))   # (HF2D_SO_NAME / HF2D_NVCC_EXTRA: tuning experiments)
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-fmad=false", "-std=c++17",
               "-shared", "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
 
@@ -31,7 +31,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         if os.path.exists(SO):
             return SO   # GPU box without a toolchain: use the prebuilt library that travelled with the snapshot
         raise RuntimeError("nvcc not found and no prebuilt libhf2d_gpu.so")
-    cmd = [nvcc] + NVCC_FLAGS + ["-o", SO, os.path.join(CSRC, "hf2d_gpu.cu")]
+    cmd = [nvcc] + NVCC_FLAGS + os.environ.get("HF2D_NVCC_EXTRA", "").split() + ["-o", SO, os.path.join(CSRC, "hf2d_gpu.cu")]
     r = subprocess.run(cmd, capture_output=True, text=True)
     log = r.stdout + r.stderr
     with open(os.path.join(HERE, "build.log"), "w") as f:

@@ -41,35 +41,73 @@ template <int NS, int AXI, int TTC> struct KCfg {
     static constexpr bool plain = TTC >= 0;
 };
 
+// Where a node's own Stage-2 inputs come from.  General tiles read the planes directly; plain tiles read the warp's
+// staged copy of the column in shared memory (hf2d_stage2.cuh), filled by cp.async one column ahead of the sweep.
+enum { PL_S = 0, PL_SN = NEQ, PL_U = 2 * NEQ, PL_V, PL_TG, PL_CP, PL_R, PL_KG, PL_P, PL_MU, PL_MUT, PL_LAM, PL_LMIN, PL_COUNT };
+#define TILE_ROWS 33   // 31 owned rows + the halo row below + the row above (up neighbour of the last owner)
+struct GlobalLoad {
+    const Params& P; long long m;
+    __device__ __forceinline__ double S(int k) const { return P.S_in[(long long)k * P.N + m]; }
+    __device__ __forceinline__ double SN(int k) const { return P.SN[(long long)k * P.N + m]; }
+    __device__ __forceinline__ double U() const { return P.U_in[m]; }
+    __device__ __forceinline__ double V() const { return P.V_in[m]; }
+    __device__ __forceinline__ double Tg() const { return P.Tg_in[m]; }
+    __device__ __forceinline__ double CP() const { return P.CP_in[m]; }
+    __device__ __forceinline__ double R() const { return P.R_in[m]; }
+    __device__ __forceinline__ double kg() const { return P.kg_in[m]; }
+    __device__ __forceinline__ double p() const { return P.p[m]; }
+    __device__ __forceinline__ double mu() const { return P.mu_in[m]; }
+    __device__ __forceinline__ double mu_t() const { return P.mu_t[m]; }
+    __device__ __forceinline__ double lam() const { return P.lam[m]; }
+    __device__ __forceinline__ double lmin() const { return P.l_min[m]; }
+};
+struct TileLoad {
+    const double* t;   // this lane's element of plane 0 of the staged column; planes are TILE_ROWS doubles apart
+    __device__ __forceinline__ double pl(int q) const { return t[q * TILE_ROWS]; }
+    __device__ __forceinline__ double S(int k) const { return pl(PL_S + k); }
+    __device__ __forceinline__ double SN(int k) const { return pl(PL_SN + k); }
+    __device__ __forceinline__ double U() const { return pl(PL_U); }
+    __device__ __forceinline__ double V() const { return pl(PL_V); }
+    __device__ __forceinline__ double Tg() const { return pl(PL_TG); }
+    __device__ __forceinline__ double CP() const { return pl(PL_CP); }
+    __device__ __forceinline__ double R() const { return pl(PL_R); }
+    __device__ __forceinline__ double kg() const { return pl(PL_KG); }
+    __device__ __forceinline__ double p() const { return pl(PL_P); }
+    __device__ __forceinline__ double mu() const { return pl(PL_MU); }
+    __device__ __forceinline__ double mu_t() const { return pl(PL_MUT); }
+    __device__ __forceinline__ double lam() const { return pl(PL_LAM); }
+    __device__ __forceinline__ double lmin() const { return pl(PL_LMIN); }
+};
+
 // The part of local_update that follows the commit loop: L.S[] holds the committed S of node m.
 // FULL=false computes only what neighbours read (S[0], S[4..8] post-chemistry, U, V, Tg).
-template <class KC, bool FULL>
-__device__ __forceinline__ void local_rest(const Params& P, const StepState& st, long long m, uint32_t ct, uint32_t tt, Local& L) {
+template <class KC, bool FULL, class D, class LD>
+__device__ __forceinline__ void local_rest(D& dv, const LD& ld, const Params& P, const StepState& st, long long m, uint32_t ct, uint32_t tt, Local& L) {
     const bool act = node_active(ct);
     const bool fc = !act && is_set(ct, NT_FC) && !is_set(ct, CT_SOLID);
     L.active = act; L.fc = fc; L.filled = false;
     // NT_FC nodes always run FillNode2D(1,0,...) (deeps2d_core.cpp:1331), active nodes follow TurbStartIter (:1240-1244)
     const int is_init = fc ? 0 : st.is_init;
     L.s7c = L.S[7]; L.s8c = L.S[8];
-    L.Uo = P.U_in[m]; L.Vo = P.V_in[m]; L.Tgo = P.Tg_in[m];
+    L.Uo = ld.U(); L.Vo = ld.V(); L.Tgo = ld.Tg();
     L.U = L.Uo; L.V = L.Vo; L.Tg = L.Tgo;
-    L.CP = P.CP_in[m]; L.R = P.R_in[m];
-    L.mu = KC::ns ? P.mu_in[m] : 0.;
-    const double kg_old = P.kg[m];
+    L.CP = ld.CP(); L.R = ld.R();
+    L.mu = KC::ns ? ld.mu() : 0.;
+    const double kg_old = ld.kg();
     L.kg = kg_old;
-    if (FULL) { L.po = P.p[m]; L.p = L.po; }
+    if (FULL) { L.po = ld.p(); L.p = L.po; }
     if (!act && !fc) { L.y4 = L.S[4]; L.y5 = L.S[5]; L.y6 = L.S[6]; return; }
     // ---- FillNode2D, local part (hyper_flow_node.hpp:382-492) ----
     if (!(L.S[iRho] == 0) && !(kg_old < 1)) {
         L.filled = true;
-        L.kg = ddiv(L.CP, L.CP - L.R);
-        if (is_set(ct, CT_U_CONST)) L.S[iRhoU] = L.U * L.S[iRho]; else L.U = ddiv(L.S[iRhoU], L.S[iRho]);
-        if (is_set(ct, CT_V_CONST)) L.S[iRhoV] = L.V * L.S[iRho]; else L.V = ddiv(L.S[iRhoV], L.S[iRho]);
+        L.kg = dv.div(L.CP, L.CP - L.R);
+        if (is_set(ct, CT_U_CONST)) L.S[iRhoU] = L.U * L.S[iRho]; else L.U = dv.div(L.S[iRhoU], L.S[iRho]);
+        if (is_set(ct, CT_V_CONST)) L.S[iRhoV] = L.V * L.S[iRho]; else L.V = dv.div(L.S[iRhoV], L.S[iRho]);
         if (KC::ns && (tt & TT_MASK) != 0) {
             // the S-rewriting part of TurbModRANS2D (:753-779 k-eps, :856-862 SA)
             if (is_set(tt, TCT_Prandtl_Model)) {
             } else if (is_set(tt, TCT_k_eps_Model)) {
-                const double l = OMAX(P.l_min[m], OMIN(P.dy, P.dx)) * 0.41;
+                const double l = OMAX(ld.lmin(), OMIN(P.dy, P.dx)) * 0.41;
                 const double p34 = (P.tem == TEM_k_eps_RNG) ? P.pow_cmu_34[1] : P.pow_cmu_34[0];
                 if (is_init) {
                     const double TmpI = P.turb_I * sqrt(L.U * L.U + L.V * L.V + 1.e-30);
@@ -97,8 +135,8 @@ __device__ __forceinline__ void local_rest(const Params& P, const StepState& st,
             Tmp1 = sqrt(L.U * L.U + L.V * L.V + 1.e-30);
             L.S[iRhoU] = Tmp1 * sp.BGX;
             L.S[iRhoV] = Tmp1 * sp.BGY;
-            L.U = ddiv(L.S[iRhoU], L.S[iRho]);
-            L.V = ddiv(L.S[iRhoV], L.S[iRho]);
+            L.U = dv.div(L.S[iRhoU], L.S[iRho]);
+            L.V = dv.div(L.S[iRhoV], L.S[iRho]);
         } else if (is_set(ct, CT_WALL_NO_SLIP)) {
             const SpecNode& sp = P.spec[P.spec_idx[m]];
             if (FULL) { L.Upre = L.S[iRhoU] / L.S[iRho]; L.Vpre = L.S[iRhoV] / L.S[iRho]; }
@@ -107,22 +145,22 @@ __device__ __forceinline__ void local_rest(const Params& P, const StepState& st,
             L.S[iRhoV] = L.V * L.S[iRho];
         }
         const double pp = (L.kg - 1.) * (L.S[iRhoE] - L.S[iRho] * (L.U * L.U + L.V * L.V) * 0.5 - Tmp3);
-        L.Tg = ddiv(ddiv(pp, L.R), L.S[iRho]);
+        L.Tg = dv.div(dv.div(pp, L.R), L.S[iRho]);
         if (FULL) L.p = pp;
     }
     // ---- species part of CalcChemicalReactions (deeps2d_core.cpp:4702-4728, 4748-4777); active nodes only ----
     L.y4 = L.S[4]; L.y5 = L.S[5]; L.y6 = L.S[6];
     if (act) {
-        double Yfu = ddiv(L.S[iYfu], L.S[0]), Yox = ddiv(L.S[iYox], L.S[0]), Ycp = ddiv(L.S[iYcp], L.S[0]);
+        double Yfu = dv.div(L.S[iYfu], L.S[0]), Yox = dv.div(L.S[iYox], L.S[0]), Ycp = dv.div(L.S[iYcp], L.S[0]);
         double Yair = 1. - (Yfu + Yox + Ycp);
         const bool yconst = is_set(ct, CT_Y_CONST);
         if (!yconst) {
-            double Y0 = ddiv(1., Yfu + Yox + Ycp + Yair);
+            double Y0 = dv.div(1., Yfu + Yox + Ycp + Yair);
             Yfu = Yfu * Y0; Yox = Yox * Y0; Ycp = Ycp * Y0;
             const double Tf = P.tf_uniform ? P.Tf0 : P.Tf[m];
             if (L.Tg > Tf) {
                 if (Yox > Yfu * P.K0) { Yox = Yox - Yfu * P.K0; Yfu = 0.; Ycp = 1. - Yox - Yair; }
-                else { Yfu = Yfu - ddiv(Yox, P.K0); Yox = 0.; Ycp = 1. - Yfu - Yair; }
+                else { Yfu = Yfu - dv.div(Yox, P.K0); Yox = 0.; Ycp = 1. - Yfu - Yair; }
             }
         }
         if (FULL) { L.Yfu = Yfu; L.Yox = Yox; L.Ycp = Ycp; L.Yair = Yair; }
@@ -130,7 +168,7 @@ __device__ __forceinline__ void local_rest(const Params& P, const StepState& st,
         if (Ycp < 1.e-8) Ycp = 0.;
         if (Yox < 1.e-8) Yox = 0.;
         if (Yfu < 1.e-8) Yfu = 0.;
-        const double Y0 = ddiv(1., Yfu + Yox + Ycp + Yair);
+        const double Y0 = dv.div(1., Yfu + Yox + Ycp + Yair);
         Yfu = Yfu * Y0; Yox = Yox * Y0; Ycp = Ycp * Y0; Yair = Yair * Y0;
         if (FULL) { L.Y[0] = Yfu; L.Y[1] = Yox; L.Y[2] = Ycp; L.Y[3] = Yair; }
         if (!yconst) { L.y4 = fabs(Yfu * L.S[0]); L.y5 = fabs(Yox * L.S[0]); L.y6 = fabs(Ycp * L.S[0]); }

@@ -18,8 +18,9 @@ __global__ void k_begin_step(Params P) {
     s->dt = dtm;                                                     // deeps2d_core.cpp:803 (serial rule)
     if (P.dt_rule == 1) s->dt_min_bits = d2bits(1.0);               // MPI rule: per-step minimum (:850)
     const double it = (double)s->iter;
-    s->beta_scn = tab_get(&P.tab[13], it);
-    s->CFL_scn = tab_get(&P.tab[12], it);
+    DivExact dv;
+    s->beta_scn = tab_get(dv, &P.tab[13], it);
+    s->CFL_scn = tab_get(dv, &P.tab[12], it);
     if ((int)s->iter < P.TurbStartIter) { s->is_mu_t = 0; s->is_init = P.isTurbulenceReset; }
     else { s->is_mu_t = 1; s->is_init = 0; }
     for (int k = 0; k < NEQ; k++) { s->RMS[k] = 0.; s->sumDiv[k] = 0.; s->iRMS[k] = 0ull; s->DDmax_bits[k] = 0ull; }

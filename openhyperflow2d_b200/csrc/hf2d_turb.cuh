@@ -19,12 +19,12 @@ struct TurbOut {
 // the reference's pow(double,int) is __builtin_powi, expanded by g++ as x^3*x^3 with x^3=(x*x)*x (oracle/deeps2d_oracle.c)
 __device__ __forceinline__ double powi6(double x) { const double x3 = (x * x) * x; return x3 * x3; }
 
-template <class KC>
-__device__ __forceinline__ void turb_own(const Params& P, const StepState& st, long long m, uint32_t ct, uint32_t tt,
+template <class KC, class D, class LD>
+__device__ __forceinline__ void turb_own(D& dv, const LD& ld, const Params& P, const StepState& st, long long m, uint32_t ct, uint32_t tt,
                                          const Local& L, const Grads& g, double yj, TurbOut& T) {
     const double rho = L.S[iRho];
     const int is_init = st.is_init, is_mu_t = st.is_mu_t, tem = P.tem;
-    const double l_min = P.l_min[m];
+    const double l_min = ld.lmin();
     double l = OMAX(l_min, OMIN(P.dy, P.dx)) * 0.41;
     if (is_set(tt, TCT_Prandtl_Model)) {
         const double n_0 = l_min * 0.41, A_p = 26.;
@@ -41,12 +41,12 @@ __device__ __forceinline__ void turb_own(const Params& P, const StepState& st, l
         const double Tmp1 = g.dUdy + g.dVdx;
         const double Tmp2 = rho * l;
         double Tmp3 = g.dUdx * g.dUdx + g.dVdy * g.dVdy;
-        if (KC::axi) Tmp3 += ddiv(L.U, yj);
+        if (KC::axi) Tmp3 += dv.div(L.U, yj);
         if (T.mu_t == 0) T.mu_t = rho * l * l * OMAX(fabs(g.dUdy), fabs(g.dVdx));
         G = T.mu_t * (Tmp1 * Tmp1 + 2 * Tmp3);
         // Rt and the damping functions see S[k], S[eps] as committed, before this call's boundary rewrites
         if (tem == TEM_k_eps_Chien || tem == TEM_k_eps_JL || tem == TEM_k_eps_LSY) {   // (the only variants that read Rt)
-            if (L.s8c != 0.0 && L.mu != 0.0) Rt = ddiv(ddiv(L.s7c * L.s7c, L.s8c), L.mu); else Rt = 0;
+            if (L.s8c != 0.0 && L.mu != 0.0) Rt = dv.div(dv.div(L.s7c * L.s7c, L.s8c), L.mu); else Rt = 0;
         }
         if (tem == TEM_k_eps_Std) {
         } else if (tem == TEM_k_eps_Chien) {
@@ -54,26 +54,26 @@ __device__ __forceinline__ void turb_own(const Params& P, const StepState& st, l
             C1eps = 1.35; C2eps = 1.8;
             f2 = 1.0 - 0.4 / 1.8 * exp(-(Rt * Rt) / 36.0);
             f_mu = 1.0 - exp(-0.0115 * yp);
-            L_k = ddiv(-2.0 * L.mu * L.s7c, Tmp2 * Tmp2);
-            L_eps = ddiv(-2.0 * L.mu * L.s8c, Tmp2 * Tmp2) * exp(-yp / 2.0);
-            Mt = ddiv(ddiv(1.5 * L.s7c, L.kg), L.po);
+            L_k = dv.div(-2.0 * L.mu * L.s7c, Tmp2 * Tmp2);
+            L_eps = dv.div(-2.0 * L.mu * L.s8c, Tmp2 * Tmp2) * exp(-yp / 2.0);
+            Mt = dv.div(dv.div(1.5 * L.s7c, L.kg), L.po);
         } else if (tem == TEM_k_eps_JL) {
             f_mu = exp(-2.5 / (1.0 + Rt / 50));
         } else if (tem == TEM_k_eps_LSY) {
             f_mu = exp(-3.4 / (1.0 + Rt / 50.0) / (1.0 + Rt / 50.0));
         } else if (tem == TEM_k_eps_RNG) {
             const double nu_0 = 4.38;
-            if (L.s8c != 0.) nu = ddiv(dsqrt(G) * L.s7c, L.s8c); else nu = 0;
+            if (L.s8c != 0.) nu = dv.div(dv.sqrt(G) * L.s7c, L.s8c); else nu = 0;
             C_mu = 0.0845; C1eps = 1.42;
-            C2eps = 1.68 + ddiv(C_mu * nu * nu * nu * (1.0 - ddiv(nu, nu_0)), 1. + 0.012 * nu * nu * nu);
+            C2eps = 1.68 + dv.div(C_mu * nu * nu * nu * (1.0 - dv.div(nu, nu_0)), 1. + 0.012 * nu * nu * nu);
             sig_k = 0.7194; sig_eps = 0.7194; f_mu = 1.;
         }
         const double S7 = L.S[iK], S8 = L.S[iEps];   // after the rewrites
-        if (is_init) { if (S8 != 0) T.mu_t = fabs(ddiv(C_mu * f_mu * S7 * S7, S8)); }
-        if (is_mu_t && S8 != 0) { const double nu_t = fabs(ddiv(C_mu * f_mu * S7 * S7, S8)); T.mu_t = OMIN(nu_t, T.mu_t); }
+        if (is_init) { if (S8 != 0) T.mu_t = fabs(dv.div(C_mu * f_mu * S7 * S7, S8)); }
+        if (is_mu_t && S8 != 0) { const double nu_t = fabs(dv.div(C_mu * f_mu * S7 * S7, S8)); T.mu_t = OMIN(nu_t, T.mu_t); }
         if (!is_init) {
             T.A7 = S7 * L.U; T.A8 = S8 * L.U; T.B7 = S7 * L.V; T.B8 = S8 * L.V;
-            const double mk = ddiv(T.mu_t, sig_k), me = ddiv(T.mu_t, sig_eps);
+            const double mk = dv.div(T.mu_t, sig_k), me = dv.div(T.mu_t, sig_eps);
             const double RX7 = (L.mu + mk) * g.dkdx, RX8 = (L.mu + me) * g.depsdx;
             const double RY7 = (L.mu + mk) * g.dkdy, RY8 = (L.mu + me) * g.depsdy;
             T.A7 = T.A7 - RX7; T.A8 = T.A8 - RX8; T.B7 = T.B7 - RY7; T.B8 = T.B8 - RY8;
@@ -82,13 +82,13 @@ __device__ __forceinline__ void turb_own(const Params& P, const StepState& st, l
                 T.zSrcAdd78 = true;
                 if (!is_set(tt, TCT_k_CONST)) { T.Src7 = (G - S8 * (1 + Mt) + L_k * rho); T.wSrc7 = true; }
                 if (!is_set(tt, TCT_eps_CONST) && S7 != 0) {
-                    T.Src8 = (ddiv(C1eps * f1 * S8, S7) * G - ddiv(C2eps * f2 * S8 * S8, S7) + L_eps * rho); T.wSrc8 = true;
+                    T.Src8 = (dv.div(C1eps * f1 * S8, S7) * G - dv.div(C2eps * f2 * S8 * S8, S7) + L_eps * rho); T.wSrc8 = true;
                 }
             }
             // TurbulenceAxisymmAddOn (:242-252)
             if (KC::axi) {
                 const double FT = (double)KC::axi;
-                T.F7 = FT * (L.mu + T.mu_t) * g.dkdy; T.F8 = FT * (L.mu + ddiv(T.mu_t, 1.3)) * g.depsdy; T.wF7 = T.wF8 = true;
+                T.F7 = FT * (L.mu + T.mu_t) * g.dkdy; T.F8 = FT * (L.mu + dv.div(T.mu_t, 1.3)) * g.depsdy; T.wF7 = T.wF8 = true;
             }
         }
     } else if (is_set(tt, TCT_SA_Model)) {
@@ -100,25 +100,25 @@ __device__ __forceinline__ void turb_own(const Params& P, const StepState& st, l
             const double Cw1 = Cb1 / (_k * _k) + (1 + Cb2) / sig;
             const double Cw2 = 0.3, Cw3 = 2.0, Cv1 = 7.1, Ct2 = 2.0, Ct4 = 0.5, C5 = 3.5;
             const double a_sound2 = L.kg * L.R * L.Tgo;     // new k, lagged R, last step's Tg (FillNode2D order)
-            const double nu = ddiv(L.mu, rho);
-            const double ksi = ddiv(S7, nu);
-            fv1 = ddiv(ksi * ksi * ksi, ksi * ksi * ksi + Cv1 * Cv1 * Cv1);
-            const double nu_hat = ddiv(ddiv(T.mu_t, rho), fv1);
-            const double fv2 = 1.0 - ddiv(ksi, 1.0 + ksi * fv1);
+            const double nu = dv.div(L.mu, rho);
+            const double ksi = dv.div(S7, nu);
+            fv1 = dv.div(ksi * ksi * ksi, ksi * ksi * ksi + Cv1 * Cv1 * Cv1);
+            const double nu_hat = dv.div(dv.div(T.mu_t, rho), fv1);
+            const double fv2 = 1.0 - dv.div(ksi, 1.0 + ksi * fv1);
             const double Wxy = 0.5 * (g.dVdx - g.dUdy);
-            const double Omega = dsqrt(2.0 * Wxy * Wxy);
-            double S_hat = Omega + ddiv(S7, _k * _k * l_min * l_min) * fv2;
+            const double Omega = dv.sqrt(2.0 * Wxy * Wxy);
+            double S_hat = Omega + dv.div(S7, _k * _k * l_min * l_min) * fv2;
             if (S_hat < 0.3 * Omega) S_hat = 0.3 * Omega;
-            const double r = OMIN((ddiv(S7, S_hat * _k * _k * l_min * l_min)), 10.0);
+            const double r = OMIN((dv.div(S7, S_hat * _k * _k * l_min * l_min)), 10.0);
             const double gg = r + Cw2 * (pow(r, 6.0) - r);
             const double fw = gg * pow((1.0 + pow(Cw3, 6.0)) / (pow(gg, 6.0) + pow(Cw3, 6.0)), 1.0 / 6.0);
             const double ft2 = Ct2 * exp(-Ct4 * ksi * ksi);
             T.A7 = S7 * L.U; T.B7 = S7 * L.V;
             const double Div_nu = (g.dkdx + g.dkdy);
-            const double RX7 = ddiv((nu + S7) * g.dkdx, sig), RY7 = ddiv((nu + S7) * g.dkdy, sig);
+            const double RX7 = dv.div((nu + S7) * g.dkdx, sig), RY7 = dv.div((nu + S7) * g.dkdy, sig);
             T.A7 = T.A7 - RX7; T.B7 = T.B7 - RY7; T.wAB7 = true;
-            T.Src7 = Cb1 * (1.0 - ft2) * S_hat * S7 - (Cw1 * fw - Cb1 / (_k * _k) * ft2) * ddiv(S7, l_min) * ddiv(S7, l_min) +
-                     ddiv(Cb2 * Div_nu * Div_nu, sig) - ddiv(C5 * nu_hat * nu_hat, a_sound2) * g.dUdy * g.dVdx;
+            T.Src7 = Cb1 * (1.0 - ft2) * S_hat * S7 - (Cw1 * fw - Cb1 / (_k * _k) * ft2) * dv.div(S7, l_min) * dv.div(S7, l_min) +
+                     dv.div(Cb2 * Div_nu * Div_nu, sig) - dv.div(C5 * nu_hat * nu_hat, a_sound2) * g.dUdy * g.dVdx;
             T.wSrc7 = true;
         }
         // TurbulenceAxisymmAddOn
@@ -132,7 +132,7 @@ __device__ __forceinline__ void turb_own(const Params& P, const StepState& st, l
     } else if (is_set(tt, TCT_Smagorinsky_Model)) {
         const double Cs = 0.1, _delta = sqrt(P.dx * P.dy);
         const double Wxy = 0.5 * (g.dVdx - g.dUdy);
-        const double Omega = dsqrt(2.0 * Wxy * Wxy);
+        const double Omega = dv.sqrt(2.0 * Wxy * Wxy);
         if (is_mu_t) { T.mu_t = OMAX(0, (rho * (Cs * _delta) * (Cs * _delta) * Omega)); T.lam_t = T.mu_t * L.CP; T.w_lam_t = true; }
     }
 }

@@ -54,11 +54,17 @@ if len(lines) != len(body):
     print(f"warning: {len(lines)} disassembled instructions vs {len(body)} profiled", file=sys.stderr)
 n = min(len(lines), len(body))
 by_line = collections.Counter(); samp = collections.Counter(); by_op = collections.Counter(); by_file = collections.Counter()
+stall_cols = [h for h in hdr if h.startswith("stall_") and "Not Issued" not in h]
+by_reason = collections.Counter(); line_reason = collections.defaultdict(collections.Counter)
 tot = 0
 for (loc, ins), r in zip(lines[:n], body[:n]):
     ex = int(r[ci["Instructions Executed"]] or 0)
     sm = int(r[ci["# Samples"]] or 0)
     by_line[loc] += ex; samp[loc] += sm; by_file[loc[0]] += ex
+    for h in stall_cols:
+        v = int(r[ci[h]] or 0)
+        if v:
+            by_reason[h] += v; line_reason[loc][h] += v
     op = re.sub(r"^@!?U?P\d+\s+", "", ins).split()[0].split(".")[0]
     by_op[op] += ex
     tot += ex
@@ -69,3 +75,11 @@ print("-- by line (instructions, samples)")
 ts = sum(samp.values()) or 1
 for k, v in by_line.most_common(top):
     print(f"{v:12d} {100 * v / tot:5.1f}%  samples {100 * samp[k] / ts:5.1f}%  {k[0]}:{k[1]}")
+print("-- stall samples by reason")
+tr = sum(by_reason.values()) or 1
+for k, v in by_reason.most_common(10):
+    print(f"{100 * v / tr:5.1f}%  {k}")
+print("-- lines by stall samples (dominant reasons)")
+for k, v in samp.most_common(top):
+    rs = ", ".join(f"{a.replace('stall_', '')} {100 * b / max(v, 1):.0f}%" for a, b in line_reason[k].most_common(3))
+    print(f"samples {100 * v / ts:5.1f}%  instr {100 * by_line[k] / tot:5.1f}%  {k[0]}:{k[1]}  [{rs}]")
