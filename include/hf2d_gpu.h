@@ -132,13 +132,15 @@ int  hf2d_gpu_tile_counts(hf2d_gpu* h, int* n_plain, int* n_general, int* tile_c
 int  hf2d_gpu_bytes_per_cell(hf2d_gpu* h, double* bytes);
 
 /* Multi-GPU (X-slabs, one process per GPU): pack the columns the neighbours need into `buf` / consume received
- * ones.  side: 0 = left neighbour, 1 = right neighbour.  phase: 0 = before Stage 1, 1 = between the two halves
- * of Stage 2 (see DESIGN.md "seams").  `buf` is device memory of hf2d_gpu_halo_bytes() bytes. */
+ * ones.  side: 0 = left neighbour, 1 = right neighbour.  phase: 0 = full edge columns after Stage 2 (both ways),
+ * 1 = shadow S of the edge column between Stage 1 and Stage 2 (left -> right), 2 = S of the edge column after the
+ * Neumann pre-pass (left -> right; makes Neumann chains that cross a seam exact) -- see DESIGN.md "seams".  `buf` is device memory of hf2d_gpu_halo_bytes() bytes. */
 size_t hf2d_gpu_halo_bytes(hf2d_gpu* h, int phase);
 int  hf2d_gpu_halo_pack(hf2d_gpu* h, int side, int phase, void* dev_buf);
 int  hf2d_gpu_halo_unpack(hf2d_gpu* h, int side, int phase, const void* dev_buf);
 /* Split step for drivers that exchange halos between phases: begin (dt, scenario), stage1, stage2, end. */
 int  hf2d_gpu_step_begin(hf2d_gpu* h);
+int  hf2d_gpu_step_prepass(hf2d_gpu* h);   /* optional: the ordered Neumann pre-pass alone; stage1 then skips it (halo phase 2) */
 int  hf2d_gpu_step_stage1(hf2d_gpu* h);
 int  hf2d_gpu_step_stage2(hf2d_gpu* h);
 int  hf2d_gpu_step_end(hf2d_gpu* h, hf2d_step_report* report /* may be NULL: no read-back */);

@@ -62,7 +62,7 @@ _lib = None
 EXPORTS = ["hf2d_gpu_last_error", "hf2d_gpu_device_count", "hf2d_gpu_create", "hf2d_gpu_destroy", "hf2d_gpu_upload_aos",
            "hf2d_gpu_download_aos", "hf2d_gpu_step", "hf2d_gpu_run_cycle", "hf2d_gpu_field_ptr", "hf2d_gpu_active_cells",
            "hf2d_gpu_bytes_per_cell", "hf2d_gpu_tile_counts", "hf2d_gpu_halo_bytes", "hf2d_gpu_halo_pack", "hf2d_gpu_halo_unpack", "hf2d_gpu_step_begin",
-           "hf2d_gpu_step_stage1", "hf2d_gpu_step_stage2", "hf2d_gpu_step_end", "hf2d_gpu_dt_ptr", "hf2d_gpu_stream",
+           "hf2d_gpu_step_prepass", "hf2d_gpu_step_stage1", "hf2d_gpu_step_stage2", "hf2d_gpu_step_end", "hf2d_gpu_dt_ptr", "hf2d_gpu_stream",
            "hf2d_gpu_set_stream", "hf2d_gpu_dt_export", "hf2d_gpu_dt_import", "hf2d_gpu_launch_count"]
 
 
@@ -86,7 +86,7 @@ def lib():
         L.hf2d_gpu_halo_bytes.restype = C.c_size_t
         L.hf2d_gpu_halo_pack.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.hf2d_gpu_halo_unpack.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
-        for f in ("hf2d_gpu_step_begin", "hf2d_gpu_step_stage1", "hf2d_gpu_step_stage2"):
+        for f in ("hf2d_gpu_step_begin", "hf2d_gpu_step_prepass", "hf2d_gpu_step_stage1", "hf2d_gpu_step_stage2"):
             getattr(L, f).argtypes = [C.c_void_p]
         L.hf2d_gpu_step_end.argtypes = [C.c_void_p, C.POINTER(StepReport)]
         L.hf2d_gpu_dt_ptr.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
@@ -223,6 +223,9 @@ class Solver:
 
     def step_begin(self):
         _ck(lib().hf2d_gpu_step_begin(self._h))
+
+    def step_prepass(self):
+        _ck(lib().hf2d_gpu_step_prepass(self._h))
 
     def step_stage1(self):
         _ck(lib().hf2d_gpu_step_stage1(self._h))

@@ -52,7 +52,10 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 #define S2_TILE_DOUBLES (PL_COUNT * TILE_ROWS)          // one staged column of one warp
 #define S2_WARPS 4               // warps (strips) per block
-#define S2_DYN_SMEM_PLAIN (S2_WARPS * 2 * S2_TILE_DOUBLES * 8)
+#ifndef S2_STAGE
+#define S2_STAGE 1               // 1: plain tiles stage their columns in shared memory with cp.async
+#endif
+#define S2_DYN_SMEM_PLAIN (S2_STAGE ? S2_WARPS * 2 * S2_TILE_DOUBLES * 8 : 0)
 #define S2_THREADS (32 * S2_WARPS)
 // STRIP_ROWS (31, hf2d_stage1.cuh): rows a warp owns; lane 0 is the halo row below them
 
@@ -69,6 +72,8 @@ __global__ void __launch_bounds__(S2_THREADS, KC::plain ? S2_MINB_PLAIN : S2_MIN
 k_stage2(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI, int want_rms) {
     __shared__ double sh_acc[S2_WARPS][2 * NEQ];               // RMS, sumDiv partial sums of the warp (want_rms steps)
     __shared__ unsigned long long sh_u[S2_WARPS][2 * NEQ + 2]; // counts, max DD, dt-min, first error
+    __shared__ SmemTables sh_tab;
+    if (S2_SMEM_TABLES) smem_tables_fill(sh_tab, P.tab);
     StepState st = *P.st;         // snapshot (the accumulators are only touched through atomics)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int t_idx = blockIdx.x * S2_WARPS + warp;
@@ -119,7 +124,8 @@ k_stage2(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI,
         cp_async_commit();
     };
     int cur = 0;
-    if constexpr (KC::plain) { if (i_first < i1) { stage_column(i_first, 0); cp_async_wait_all(); __syncwarp(); } }
+    constexpr bool STAGED = KC::plain && S2_STAGE;
+    if constexpr (STAGED) { if (i_first < i1) { stage_column(i_first, 0); cp_async_wait_all(); __syncwarp(); } }
 
     // A phase is run with the branch-free DivFast policy on plain tiles and re-run exactly when any lane asks for it
     auto run = [&](auto&& ph) {
@@ -134,11 +140,11 @@ k_stage2(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI,
     for (int i = i_first; i < i1; i++) {
         const bool own_col = i >= i0;
         const long long n = valid_j ? (long long)i * ny + j : 0;
-        using LD = std::conditional_t<KC::plain, TileLoad, GlobalLoad>;
+        using LD = std::conditional_t<STAGED, TileLoad, GlobalLoad>;
         const double* const tcur = tile0 + cur * S2_TILE_DOUBLES + lane;
         const double* const tnxt = tile0 + (cur ^ 1) * S2_TILE_DOUBLES + lane;
-        LD ld = [&]() { if constexpr (KC::plain) return TileLoad{tcur}; else return GlobalLoad{P, n}; }();
-        if constexpr (KC::plain) { if (i + 1 < P.nx) stage_column(i + 1, cur ^ 1); }   // next column: own inputs then, right neighbour now
+        LD ld = [&]() { if constexpr (STAGED) return TileLoad{tcur}; else return GlobalLoad{P, n}; }();
+        if constexpr (STAGED) { if (i + 1 < P.nx) stage_column(i + 1, cur ^ 1); }   // next column: own inputs then, right neighbour now
         uint32_t ct, tt;
         if (KC::plain) { ct = CT_NODE_IS_SET; tt = (uint32_t)KC::ttc | TT_IDXL | TT_IDXR | TT_IDYU | TT_IDYD; }
         else { ct = 0; tt = 0; if (valid_j) { ct = P.ct[n]; tt = P.tt[n]; } }
@@ -153,25 +159,19 @@ k_stage2(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI,
         mine.rho = mine.y4 = mine.y5 = mine.y6 = mine.s7 = mine.s8 = mine.U = mine.V = mine.Tg = 0.;
         // ---- commit (:1156-1164) fused with the residual and the locally adaptive blending factor (:1062-1154) ----
         if constexpr (KC::plain) {
-            // every equation k < NE_C is advanced and committed; all loads are issued before the first division
-            double so[NEQ], sn[NEQ], bo[NEQ];
+            // every equation k < NE_C is advanced and committed; inputs come from the staged column at the point of use
+            double bo[NEQ];
 #pragma unroll
-            for (int k = 0; k < NEQ; k++) {
-                so[k] = 0.; sn[k] = 0.; bo[k] = 0.;
-                if (valid_j && (k < 7 || TURB_C)) {
-                    const long long o = (long long)k * N + n;
-                    so[k] = ld.S(k);
-                    if (k < NE_C) { sn[k] = ld.SN(k); if (P.bFF & 1) bo[k] = P.beta[o]; }
-                }
-            }
+            for (int k = 0; k < NEQ; k++) { bo[k] = 0.; if (valid_j && k < NE_C && (P.bFF & 1)) bo[k] = P.beta[(long long)k * N + n]; }
             auto phaseA = [&](auto& dv, auto rms) {
                 double beta_min = OMIN(P.beta0, st.beta_scn);
                 const double bb = beta_min * beta_min;
 #pragma unroll
                 for (int k = 0; k < NE_C; k++) {
-                    const bool res = upd && so[k] != 0.;
-                    const double Tmp = res ? so[k] : 1.0;
-                    const double absDD = sn[k] - so[k];
+                    const double so_k = valid_j ? ld.S(k) : 0., sn_k = valid_j ? ld.SN(k) : 0.;
+                    const bool res = upd && so_k != 0.;
+                    const double Tmp = res ? so_k : 1.0;
+                    const double absDD = sn_k - so_k;
                     const bool big = fabs(Tmp) > 1.e-15;
                     const double q = dv.div(absDD, Tmp, res && big);
                     const double DD = big ? fabs(q) : 1.0;
@@ -197,7 +197,7 @@ k_stage2(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI,
             if (want_rms) { DivExact e; phaseA(e, std::true_type()); }     // output steps only: exact policy, fused reduction
             else run([&](auto& dv) { phaseA(dv, std::false_type()); });
 #pragma unroll
-            for (int k = 0; k < NEQ; k++) L.S[k] = (k < NE_C) ? sn[k] : so[k];
+            for (int k = 0; k < NEQ; k++) L.S[k] = !valid_j ? 0. : (k < NE_C) ? ld.SN(k) : (k < 7 || TURB_C) ? ld.S(k) : 0.;
         } else {
             DivExact dv;
 #pragma unroll
@@ -267,7 +267,7 @@ k_stage2(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI,
         // values Stage 2 both reads and overwrites in place are fetched before the phase so that it can be re-run
         double mu_t0 = 0., lam0 = 0.;
         if (KC::ns && upd) { mu_t0 = ld.mu_t(); lam0 = ld.lam(); }
-        if constexpr (KC::plain) { cp_async_wait_all(); __syncwarp(); }   // column i+1 (issued before phase A) has landed
+        if constexpr (STAGED) { cp_async_wait_all(); __syncwarp(); }   // column i+1 (issued before phase A) has landed
         const unsigned long long r_dt0 = r_dt, r_err0 = r_err;
         run([&](auto& dv) {
           r_dt = r_dt0; r_err = r_err0;
@@ -284,7 +284,7 @@ k_stage2(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI,
                     NbState own, nR, nL, nU;   // `own`: a missing neighbour aliases the node itself (committed S, old U,V,Tg)
                     own.rho = L.S[iRho]; own.y4 = L.S[4]; own.y5 = L.S[5]; own.y6 = L.S[6]; own.s7 = L.s7c; own.s8 = L.s8c;
                     own.U = L.Uo; own.V = L.Vo; own.Tg = L.Tgo;
-                    if constexpr (KC::plain) {   // old state of the right / up neighbours from the staged columns
+                    if constexpr (STAGED) {   // old state of the right / up neighbours from the staged columns
                         nR.rho = tnxt[PL_S * TILE_ROWS]; nR.y4 = tnxt[(PL_S + 4) * TILE_ROWS]; nR.y5 = tnxt[(PL_S + 5) * TILE_ROWS]; nR.y6 = tnxt[(PL_S + 6) * TILE_ROWS];
                         nR.s7 = TURB_C ? tnxt[(PL_S + 7) * TILE_ROWS] : 0.; nR.s8 = TURB_C ? tnxt[(PL_S + 8) * TILE_ROWS] : 0.;
                         nR.U = tnxt[PL_U * TILE_ROWS]; nR.V = tnxt[PL_V * TILE_ROWS]; nR.Tg = tnxt[PL_TG * TILE_ROWS];
@@ -348,7 +348,7 @@ k_stage2(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI,
           }
         });
         carry = mine;
-        if constexpr (KC::plain) { __syncwarp(); cur ^= 1; }   // every lane is done with this column's buffer before it is refilled
+        if constexpr (STAGED) { __syncwarp(); cur ^= 1; }   // every lane is done with this column's buffer before it is refilled
     }
 #include "hf2d_stage2_reduce.inc"
 }

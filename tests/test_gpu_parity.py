@@ -152,3 +152,94 @@ def test_plain_tiles_match_oracle(model, nsteps):
         else:
             assert rel_linf(a, b) <= REL_TOL, f"{model}: {f} {rel_linf(a, b):.3e}"
     np.testing.assert_allclose(list(rep.sum_RMS), list(orep.sum_RMS), rtol=1e-9, atol=1e-300)
+
+
+def _slab_run(model, nx, ny, nsteps, world):
+    """`world` X-slabs on ONE GPU (one hf2d_gpu handle each, ghost columns, halo buffers handed over on the device):
+    the same call sequence SlabRunner uses across GPUs, minus the transport."""
+    import torch
+    from openhyperflow2d_b200 import cabi, gridgen
+    assert nx % world == 0
+    w = nx // world
+    Jfull, cfg, lay = gridgen.three_cylinders(nx, ny, model=model)
+    slabs = []
+    for r in range(world):
+        gl, gr = (1 if r > 0 else 0), (1 if r < world - 1 else 0)
+        J = np.array(Jfull[r * w - gl:(r + 1) * w + gr], copy=True)
+        c = dict(cfg); c["MaxX"] = J.shape[0]
+        s = cabi.Solver(c, lay, rank=r, n_ranks=world)
+        s.upload_aos(J)
+        slabs.append((s, J, gl, gr))
+    dev = torch.device("cuda", 0)
+    n0, n1 = slabs[0][0].halo_bytes(0) // 8, slabs[0][0].halo_bytes(1) // 8
+    buf0 = [[torch.zeros(n0, dtype=torch.float64, device=dev) for _ in range(2)] for _ in range(world)]
+    buf1 = [torch.zeros(n1, dtype=torch.float64, device=dev) for _ in range(world)]
+    dtb = torch.zeros(world, dtype=torch.float64, device=dev)
+    buf2 = [torch.zeros(slabs[0][0].halo_bytes(2) // 8, dtype=torch.float64, device=dev) for _ in range(world)]
+    for _ in range(nsteps):
+        for r, (s, J, gl, gr) in enumerate(slabs):      # phase 2: Neumann pre-pass left to right, overwritten edge column handed on
+            s.step_begin()
+            if gl:
+                s.halo_unpack(0, 2, buf2[r - 1].data_ptr())
+            s.step_prepass()
+            if gr:
+                s.halo_pack(1, 2, buf2[r].data_ptr())
+            torch.cuda.synchronize()
+        for s, *_ in slabs:
+            s.step_stage1()
+        torch.cuda.synchronize()
+        for r, (s, J, gl, gr) in enumerate(slabs):      # phase 1: shadow S of the last owned column -> right neighbour's left ghost
+            if gr:
+                s.halo_pack(1, 1, buf1[r].data_ptr())
+            if gl:                                      # and the overwritten S of the first owned column -> left neighbour's right ghost
+                s.halo_pack(0, 2, buf2[r].data_ptr())
+        torch.cuda.synchronize()
+        for r, (s, J, gl, gr) in enumerate(slabs):
+            if gl:
+                s.halo_unpack(0, 1, buf1[r - 1].data_ptr())
+            if gr:
+                s.halo_unpack(1, 2, buf2[r + 1].data_ptr())
+        torch.cuda.synchronize()
+        for s, *_ in slabs:
+            s.step_stage2()
+        torch.cuda.synchronize()
+        for r, (s, J, gl, gr) in enumerate(slabs):      # phase 0: full edge columns both ways
+            if gl:
+                s.halo_pack(0, 0, buf0[r][0].data_ptr())
+            if gr:
+                s.halo_pack(1, 0, buf0[r][1].data_ptr())
+        torch.cuda.synchronize()
+        for r, (s, J, gl, gr) in enumerate(slabs):
+            if gl:
+                s.halo_unpack(0, 0, buf0[r - 1][1].data_ptr())
+            if gr:
+                s.halo_unpack(1, 0, buf0[r + 1][0].data_ptr())
+        for r, (s, *_rest) in enumerate(slabs):
+            s.dt_export(dtb[r:r + 1].data_ptr())
+        torch.cuda.synchronize()
+        dtb[:] = dtb.min()
+        for r, (s, *_rest) in enumerate(slabs):
+            s.dt_import(dtb[r:r + 1].data_ptr())
+            s.step_end()
+        torch.cuda.synchronize()
+    out = np.array(Jfull, copy=True)
+    for r, (s, J, gl, gr) in enumerate(slabs):
+        s.download_aos(J)
+        out[r * w:(r + 1) * w] = J[gl:J.shape[0] - gr]
+        s.close()
+    return out, Jfull, cfg, lay
+
+
+@pytest.mark.parametrize("model", ["laminar", "keps"])
+def test_x_slabs_reproduce_single_domain(model):
+    """Two and four X-slabs with the exact-seam exchange (halo phases 2, 1, 0) give the single-domain result BIT FOR BIT,
+    including the eps equation's Neumann chain along the d/dy=0 rows that crosses every seam (k-eps)."""
+    from openhyperflow2d_b200 import cabi
+    nx, ny, nsteps = 96, 160, 5
+    ref, Jfull, cfg, lay = _slab_run(model, nx, ny, nsteps, 1)
+    for world in (2, 4):
+        got, *_ = _slab_run(model, nx, ny, nsteps, world)
+        for f in GPU_FIELDS + NS_FIELDS:
+            a, b = np.asarray(got[f], float), np.asarray(ref[f], float)
+            same = (a == b) | ((a != a) & (b != b))
+            assert same.all(), f"{model} x{world}: {f} differs in {int((~same).sum())} entries, rel-Linf {rel_linf(a, b):.3e}"
