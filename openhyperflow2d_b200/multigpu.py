@@ -1,12 +1,25 @@
 """X-slab runner: one process per GPU, ghost-column exchange + dt min-allreduce through torch.distributed (NCCL on
-GPUs, gloo in the CPU tests of the exchange logic).
+GPUs; the CPU tests drive the same exchange code over gloo with a stand-in solver).
 
 Decomposition (hf2d_start.cpp:149-175, deeps2d_core.cpp:831-840, 1336-1400): rank r owns global columns
-[r*nx, (r+1)*nx); its slab carries one ghost column per interior seam, the sweep skips ghost columns.  Per step:
-    begin -> Stage 1 -> [phase 1: our last owned column's shadow S (NextNode->S) goes to the right neighbour's left
-    ghost, so that its Stage 2 can recompute that column's NEW state exactly as the serial sweep sees it] -> Stage 2
-    -> [phase 0: full edge columns both ways] -> all-reduce(min) of the running dt -> end
-With phase 1 the result equals the single-domain serial sweep; the reference's MPI build skips it (seam-lagged).
+[r*nx, (r+1)*nx); its slab carries one ghost column per interior seam, the sweep skips ghost columns.  Per step
+(seams="exact", the default -- the result equals the single-domain serial sweep bit for bit, tests/test_gpu_parity.py):
+    begin
+    [phase 2, left -> right, in rank order]  receive the left neighbour's edge column S as its Neumann pre-pass left
+        it -> own pre-pass (hf2d_gpu_step_prepass) -> send our last owned column on: a Neumann chain that runs along a
+        whole d/dy=0 row (the eps equation) is thereby continued across the seam
+    Stage 1
+    [phase 1, left -> right]  shadow S (NextNode->S) of our last owned column -> right neighbour's left ghost, so that
+        its Stage 2 recomputes that column's NEW state exactly as the serial sweep sees it
+    [phase 2, right -> left]  S of our first owned column after the pre-pass -> left neighbour's right ghost (Stage 2
+        reads right neighbours after this step's Stage-1 overwrite)
+    Stage 2
+    [phase 0, both ways]  full edge columns for the next step
+    all-reduce(min) of the running dt -> end
+seams="lagged-chain" drops the rank-ordered phase-2 hand-off (ranks no longer wait for each other inside a step);
+a Neumann chain then restarts at each seam from the ghost column's last-step value -- the deviation is confined to
+the chain rows next to a seam (~1e-5 relative after a few steps on the three-cylinder grid).  The reference's own MPI
+build lags EVERYTHING at its seams by one step (deeps2d_core.cpp:1336-1400).
 """
 from __future__ import annotations
 
@@ -15,68 +28,57 @@ import numpy as np
 from . import cabi, gridgen
 
 
-class SlabRunner:
-    def __init__(self, nx, ny, model="keps", rank=0, world=1, device=0, exact_seams=True):
-        import torch
-        self.torch = torch
-        self.rank, self.world, self.device = rank, world, device
-        self.exact = exact_seams
-        gl = 1 if (world > 1 and rank > 0) else 0
-        gr = 1 if (world > 1 and rank < world - 1) else 0
-        self.gl, self.gr = gl, gr
-        J, cfg, lay = gridgen.three_cylinders(nx + gl + gr, ny, model=model, i0=rank * nx - gl, nx_total=nx * world)
-        self.J, self.cfg, self.layout = J, cfg, lay
-        self.solver = cabi.Solver(cfg, lay, device=device, rank=rank, n_ranks=world)
-        self.solver.set_stream(torch.cuda.current_stream().cuda_stream)
-        self.solver.upload_aos(J)
-        self.launches_last = 0
+class SlabProtocol:
+    """The per-step exchange protocol, independent of what computes: `solver` offers the split-step / halo calls of
+    cabi.Solver, buffers are torch tensors on `dev` (CUDA + NCCL in production, CPU + gloo in the protocol tests)."""
+
+    def _init_protocol(self, torch, solver, rank, world, dev, seams):
+        assert seams in ("exact", "lagged-chain")
+        self.torch, self.solver, self.rank, self.world, self.dev, self.seams = torch, solver, rank, world, dev, seams
+        self.gl = 1 if (world > 1 and rank > 0) else 0
+        self.gr = 1 if (world > 1 and rank < world - 1) else 0
         if world > 1:
-            dev = torch.device("cuda", device)
-            n0, n1 = self.solver.halo_bytes(0) // 8, self.solver.halo_bytes(1) // 8
-            self.send = [torch.zeros(n0, dtype=torch.float64, device=dev) for _ in range(2)]
-            self.recv = [torch.zeros(n0, dtype=torch.float64, device=dev) for _ in range(2)]
-            self.send1 = torch.zeros(n1, dtype=torch.float64, device=dev)
-            self.recv1 = torch.zeros(n1, dtype=torch.float64, device=dev)
-            self.dtbuf = torch.zeros(1, dtype=torch.float64, device=dev)
+            self._alloc(dev)
 
-    # ---- collectives ----
-    def barrier(self):
-        self.torch.cuda.synchronize()
-        if self.world > 1:
-            self.torch.distributed.barrier()
-            self.torch.cuda.synchronize()
+    def _alloc(self, dev):
+        torch = self.torch
+        n0, n1, n2 = (self.solver.halo_bytes(p) // 8 for p in (0, 1, 2))
+        z = lambda n: torch.zeros(n, dtype=torch.float64, device=dev)
+        self.send, self.recv = [z(n0), z(n0)], [z(n0), z(n0)]
+        self.send1, self.recv1 = z(n1), z(n1)
+        self.send2, self.recv2 = [z(n2), z(n2)], [z(n2), z(n2)]
+        self.dtbuf = z(1)
 
-    def allreduce_sum(self, v):
-        if self.world == 1:
-            return int(v)
-        t = self.torch.tensor([int(v)], dtype=self.torch.int64, device=self.torch.device("cuda", self.device))
-        self.torch.distributed.all_reduce(t)
-        return int(t.item())
+    def _batch(self, ops):
+        if ops:
+            for w in self.torch.distributed.batch_isend_irecv(ops):
+                w.wait()
 
-    def _exchange(self, phase):
-        dist = self.torch.distributed
-        s = self.solver
-        ops = []
-        if phase == 1:   # left -> right only
-            if self.gr:
-                s.halo_pack(1, 1, self.send1.data_ptr()); ops.append(dist.P2POp(dist.isend, self.send1, self.rank + 1))
-            if self.gl:
-                ops.append(dist.P2POp(dist.irecv, self.recv1, self.rank - 1))
-            if ops:
-                for w in dist.batch_isend_irecv(ops):
-                    w.wait()
-            if self.gl:
-                s.halo_unpack(0, 1, self.recv1.data_ptr())
-            return
+    def _mid_exchange(self):
+        """Between Stage 1 and Stage 2: phase 1 (left -> right) and the post-pre-pass S of the first owned column (right -> left)."""
+        dist, s, ops = self.torch.distributed, self.solver, []
+        if self.gr:
+            s.halo_pack(1, 1, self.send1.data_ptr()); ops.append(dist.P2POp(dist.isend, self.send1, self.rank + 1))
+            ops.append(dist.P2POp(dist.irecv, self.recv2[1], self.rank + 1))
+        if self.gl:
+            s.halo_pack(0, 2, self.send2[0].data_ptr()); ops.append(dist.P2POp(dist.isend, self.send2[0], self.rank - 1))
+            ops.append(dist.P2POp(dist.irecv, self.recv1, self.rank - 1))
+        self._batch(ops)
+        if self.gl:
+            s.halo_unpack(0, 1, self.recv1.data_ptr())
+        if self.gr:
+            s.halo_unpack(1, 2, self.recv2[1].data_ptr())
+
+    def _end_exchange(self):
+        """After Stage 2: phase 0, full edge columns both ways."""
+        dist, s, ops = self.torch.distributed, self.solver, []
         if self.gl:
             s.halo_pack(0, 0, self.send[0].data_ptr())
             ops += [dist.P2POp(dist.isend, self.send[0], self.rank - 1), dist.P2POp(dist.irecv, self.recv[0], self.rank - 1)]
         if self.gr:
             s.halo_pack(1, 0, self.send[1].data_ptr())
             ops += [dist.P2POp(dist.isend, self.send[1], self.rank + 1), dist.P2POp(dist.irecv, self.recv[1], self.rank + 1)]
-        if ops:
-            for w in dist.batch_isend_irecv(ops):
-                w.wait()
+        self._batch(ops)
         if self.gl:
             s.halo_unpack(0, 0, self.recv[0].data_ptr())
         if self.gr:
@@ -92,16 +94,51 @@ class SlabRunner:
         dist = self.torch.distributed
         for _ in range(n):
             s.step_begin()
+            if self.seams == "exact":     # rank-ordered hand-off of the overwritten edge column (phase 2, left -> right)
+                if self.gl:
+                    dist.recv(self.recv2[0], self.rank - 1)
+                    s.halo_unpack(0, 2, self.recv2[0].data_ptr())
+                s.step_prepass()
+                if self.gr:
+                    s.halo_pack(1, 2, self.send2[1].data_ptr())
+                    dist.send(self.send2[1], self.rank + 1)
             s.step_stage1()
-            if self.exact:
-                self._exchange(1)
+            self._mid_exchange()
             s.step_stage2()
-            self._exchange(0)
+            self._end_exchange()
             s.dt_export(self.dtbuf.data_ptr())
             dist.all_reduce(self.dtbuf, op=dist.ReduceOp.MIN)
             s.dt_import(self.dtbuf.data_ptr())
             s.step_end()
         return None
+
+class SlabRunner(SlabProtocol):
+    def __init__(self, nx, ny, model="keps", rank=0, world=1, device=0, seams="exact", rms_every=None):
+        import torch
+        self.device = device
+        gl = 1 if (world > 1 and rank > 0) else 0
+        gr = 1 if (world > 1 and rank < world - 1) else 0
+        J, cfg, lay = gridgen.three_cylinders(nx + gl + gr, ny, model=model, i0=rank * nx - gl, nx_total=nx * world)
+        self.J, self.cfg, self.layout = J, cfg, lay
+        solver = cabi.Solver(cfg, lay, device=device, rank=rank, n_ranks=world, rms_every=rms_every)
+        solver.set_stream(torch.cuda.current_stream().cuda_stream)
+        solver.upload_aos(J)
+        self.launches_last = 0
+        self._init_protocol(torch, solver, rank, world, torch.device("cuda", device), seams)
+
+    # ---- collectives ----
+    def barrier(self):
+        self.torch.cuda.synchronize()
+        if self.world > 1:
+            self.torch.distributed.barrier()
+            self.torch.cuda.synchronize()
+
+    def allreduce_sum(self, v):
+        if self.world == 1:
+            return int(v)
+        t = self.torch.tensor([int(v)], dtype=self.torch.int64, device=self.torch.device("cuda", self.device))
+        self.torch.distributed.all_reduce(t)
+        return int(t.item())
 
     def timed_steps(self, k):
         """Device time of k steps in ms: CUDA events on the stream the kernels run on, max over ranks."""

@@ -1,0 +1,150 @@
+"""CPU test (gloo, world_size 2 and 3) of the X-slab exchange protocol in openhyperflow2d_b200.multigpu.SlabProtocol.
+
+The real solver is replaced by a stand-in with the same split-step / halo interface and the same DATA DEPENDENCIES as
+the DEEPS2D step (hf2d_stage1.cuh / hf2d_stage2.cuh): an ordered in-place pre-pass whose value chains from the left
+neighbour, a Stage 1 that reads the left neighbour after and the right neighbour before that overwrite, a Stage 2 that
+reads the left neighbour's NEW state and the right neighbour's post-pre-pass state.  If any halo phase, side or
+ordering were wrong, the slabs would not reproduce the single-domain run bit for bit."""
+import ctypes as C
+import os
+import socket
+
+import numpy as np
+import pytest
+
+NY = 7
+
+
+def _view(ptr, n):
+    return np.ctypeslib.as_array((C.c_double * n).from_address(ptr))
+
+
+class FakeSolver:
+    """Columns [g0, g0+w) of a global nx_total x NY field, with ghost columns where a neighbour slab exists."""
+
+    def __init__(self, full, g0, w, rank, world):
+        self.gl, self.gr = int(rank > 0), int(rank < world - 1)
+        self.first_global = g0 == 0
+        self.S = np.array(full[g0 - self.gl:g0 + w + self.gr], copy=True)
+        self.SN = np.zeros_like(self.S)
+        self.S0 = np.zeros_like(self.S)
+        self.nx = self.S.shape[0]
+        self.lo, self.hi = self.gl, self.nx - self.gr
+        self.dt = 1.0
+
+    # --- split step ---
+    def step_begin(self):
+        self.prepass_done = False
+
+    def step_prepass(self):
+        self.S0[:] = self.S                       # pre-overwrite values (SpecNode::S0)
+        for i in range(self.lo, self.hi):         # ordered chain: left already overwritten, right not yet
+            if i == 0:
+                continue                          # global column 0 has no left neighbour
+            r = self.S0[i + 1] if i + 1 < self.nx else self.S0[i]
+            self.S[i] = (self.S[i - 1] + r) * 0.5
+        self.prepass_done = True
+
+    def step_stage1(self):
+        if not self.prepass_done:
+            self.step_prepass()
+        for i in range(self.lo, self.hi):
+            l = self.S[i - 1] if i > 0 else self.S[i]
+            r = self.S0[i + 1] if i + 1 < self.nx else self.S[i]
+            self.SN[i] = self.S[i] * 0.75 + 0.125 * (l + r) + 0.01
+
+    def step_stage2(self):
+        new = np.array(self.S, copy=True)
+        for i in range(self.lo, self.hi):
+            l_new = self.SN[i - 1] * 1.5 if i > 0 else self.SN[i] * 1.5     # left neighbour: recomputed NEW state (needs its SN)
+            r_old = self.S[i + 1] if i + 1 < self.nx else self.S[i]           # right neighbour: after this step's pre-pass
+            new[i] = self.SN[i] + 0.0625 * (r_old - l_new / 1.5)
+        self.S = new
+        self.dt = min(self.dt, float(1.0 / (1.0 + np.abs(new[self.lo:self.hi]).max())))
+
+    def step_end(self, want_report=False):
+        pass
+
+    # --- halos (include/hf2d_gpu.h: side 0 = left, 1 = right; phase 0 full column, 1 shadow S, 2 S after pre-pass) ---
+    def halo_bytes(self, phase):
+        return (2 if phase == 0 else 1) * NY * 8
+
+    def halo_pack(self, side, phase, ptr):
+        col = 1 if side == 0 else self.nx - 2
+        b = _view(ptr, self.halo_bytes(phase) // 8)
+        if phase == 0:
+            b[:NY], b[NY:] = self.S[col], self.SN[col]
+        elif phase == 1:
+            b[:] = self.SN[col]
+        else:
+            b[:] = self.S[col]
+
+    def halo_unpack(self, side, phase, ptr):
+        col = 0 if side == 0 else self.nx - 1
+        b = _view(ptr, self.halo_bytes(phase) // 8)
+        if phase == 0:
+            self.S[col], self.SN[col] = b[:NY], b[NY:]
+        elif phase == 1:
+            self.SN[col] = b
+        else:
+            self.S[col] = b
+
+    def dt_export(self, ptr):
+        _view(ptr, 1)[0] = self.dt
+
+    def dt_import(self, ptr):
+        self.dt = float(_view(ptr, 1)[0])
+
+
+def _field(nx):
+    rng = np.random.default_rng(7)
+    return rng.uniform(0.5, 2.0, size=(nx, NY))
+
+
+def _worker(rank, world, port, nx, nsteps, seams, out_dir):
+    import torch
+    import torch.distributed as dist
+    from openhyperflow2d_b200.multigpu import SlabProtocol
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    w = nx // world
+    fs = FakeSolver(_field(nx), rank * w, w, rank, world)
+    p = SlabProtocol()
+    p._init_protocol(torch, fs, rank, world, torch.device("cpu"), seams)
+    p.step(nsteps)
+    np.save(os.path.join(out_dir, f"r{rank}.npy"), np.concatenate([fs.S[fs.lo:fs.hi].ravel(), [fs.dt]]))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_exact_seams_reproduce_single_domain(world, tmp_path):
+    import torch.multiprocessing as mp
+    nx, nsteps = 12, 4
+    ref = FakeSolver(_field(nx), 0, nx, 0, 1)
+    for _ in range(nsteps):
+        ref.step_begin(); ref.step_stage1(); ref.step_stage2(); ref.step_end()
+    mp.spawn(_worker, args=(world, _free_port(), nx, nsteps, "exact", str(tmp_path)), nprocs=world, join=True)
+    got = [np.load(tmp_path / f"r{r}.npy") for r in range(world)]
+    S = np.concatenate([g[:-1] for g in got]).reshape(nx, NY)
+    assert (S == ref.S).all()
+    assert all(g[-1] == ref.dt for g in got)       # dt: min-allreduce every step
+
+
+def test_lagged_chain_differs_only_through_the_chain(tmp_path):
+    """seams="lagged-chain" drops the rank-ordered hand-off: the run completes (no rank waits on another inside the
+    pre-pass) and differs from the single-domain result, which is what the hand-off exists to prevent."""
+    import torch.multiprocessing as mp
+    nx, nsteps, world = 12, 3, 2
+    ref = FakeSolver(_field(nx), 0, nx, 0, 1)
+    for _ in range(nsteps):
+        ref.step_begin(); ref.step_stage1(); ref.step_stage2(); ref.step_end()
+    mp.spawn(_worker, args=(world, _free_port(), nx, nsteps, "lagged-chain", str(tmp_path)), nprocs=world, join=True)
+    S = np.concatenate([np.load(tmp_path / f"r{r}.npy")[:-1] for r in range(world)]).reshape(nx, NY)
+    assert not (S == ref.S).all()
+    assert np.isfinite(S).all()
