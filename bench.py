@@ -43,37 +43,59 @@ def peaks():
 
 
 class ClockSampler:
+    """SM clock and throttle reasons sampled DURING the timed region (NVML, ~5 ms period; nvidia-smi as fallback)."""
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
     def __init__(self, index=0):
-        self.rows, self.stop, self.index = [], False, index
+        self.sm, self.mx, self.reasons, self.stop, self.index = [], None, set(), False, index
         self.t = threading.Thread(target=self.run, daemon=True)
 
-    def run(self):
+    def run_nvml(self):
+        import pynvml as N
+        N.nvmlInit()
+        h = N.nvmlDeviceGetHandleByIndex(self.index)
+        self.mx = N.nvmlDeviceGetMaxClockInfo(h, N.NVML_CLOCK_SM)
+        bits = {"hw_slowdown": N.nvmlClocksThrottleReasonHwSlowdown, "hw_thermal_slowdown": N.nvmlClocksThrottleReasonHwThermalSlowdown,
+                "sw_thermal_slowdown": N.nvmlClocksThrottleReasonSwThermalSlowdown, "sw_power_cap": N.nvmlClocksThrottleReasonSwPowerCap}
+        while not self.stop:
+            self.sm.append(N.nvmlDeviceGetClockInfo(h, N.NVML_CLOCK_SM))
+            r = N.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+            for k, v in bits.items():
+                if r & v:
+                    self.reasons.add(k)
+            time.sleep(0.005)
+
+    def run_smi(self):
         while not self.stop:
             try:
                 o = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits"],
                                    capture_output=True, text=True, timeout=5).stdout.strip()
-                if o:
-                    self.rows.append([x.strip() for x in o.split(",")])
+                r = [x.strip() for x in o.split(",")]
+                if r and r[0].isdigit():
+                    self.sm.append(int(r[0])); self.mx = int(r[1])
+                    for name, col in (("hw_slowdown", 2), ("hw_thermal_slowdown", 3), ("sw_thermal_slowdown", 4), ("sw_power_cap", 5)):
+                        if len(r) > col and r[col].lower().startswith("active"):
+                            self.reasons.add(name)
             except Exception:
                 pass
-            time.sleep(0.1)
+            time.sleep(0.05)
+
+    def run(self):
+        try:
+            self.run_nvml()
+        except Exception:
+            self.run_smi()
 
     def __enter__(self):
-        self.t.start(); return self
+        self.t.start(); time.sleep(0.02); return self
 
     def __exit__(self, *a):
         self.stop = True; self.t.join(timeout=6)
 
     def summary(self):
-        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
-        reasons = []
-        for name, col in (("hw_slowdown", 2), ("hw_thermal_slowdown", 3), ("sw_thermal_slowdown", 4), ("sw_power_cap", 5)):
-            if any(len(r) > col and r[col].lower().startswith("active") for r in self.rows):
-                reasons.append(name)
-        mx = max((int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()), default=None)
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": reasons, "samples": len(sm)}
+        sm = sorted(self.sm)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_min_mhz": sm[0] if sm else None, "sm_max_mhz": self.mx,
+                "reasons": sorted(self.reasons), "samples": len(sm)}
 
 
 def cpu_baseline_port(model="keps", nx=256, ny=128, nsteps=120):
@@ -144,38 +166,54 @@ def run_reference_binary(binary, nx, ny, nsteps, threads):
 
 
 def reference_arm(args):
+    """The reference's own CPU implementation of the path on the box's host cores: the UNMODIFIED OpenMP build
+    (oracle/_ref/ohf_omp, all hardware threads) on a bounded sample of the same workload.  One solver run of a few
+    hundred DEEPS2D steps (a "step" of this arm is one of them); the number is the solver's own 'average speed' line."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     nthreads = os.cpu_count() or 1
     nx, ny = 512, 256
-    per = max(args.steps, 1)
-    best = None
-    kind, cores, how = "port", 1, ""
-    vals = []
-    for it in range(args.warmup + args.steps):
-        r = run_reference_binary("ohf_omp", nx, ny, 40, nthreads)
-        if r is None:
-            break
-        if it >= args.warmup:
-            vals.append(r)
-    if vals:
-        v = sum(x[0] for x in vals) / len(vals)
-        ser = run_reference_binary("ohf_serial", nx, ny, 40, 1)
-        kind, cores = "reference", nthreads
-        how = (f"unmodified reference (oracle/_ref/ohf_omp, OMP_NUM_THREADS={nthreads}) on a three-cylinder k-eps deck {nx}x{ny} "
-               f"({vals[0][1]} active cells), 40 steps per run, solver's own 'average speed' line; serial build: "
-               f"{ser[0]:.4g} cell-updates/s" if ser else "serial build unavailable")
-        ms = 1e3 / (sum(x[2] for x in vals) / len(vals))
+    nsteps = int(min(max(4 * (args.warmup + args.steps), 100), 400))
+    r = run_reference_binary("ohf_omp", nx, ny, nsteps, nthreads)
+    if r is not None:
+        ser = run_reference_binary("ohf_serial", nx, ny, min(nsteps, 100), 1)
+        v, kind, cores, ms = r[0], "reference", nthreads, 1e3 / r[2]
+        how = (f"unmodified reference, OpenMP build (oracle/_ref/ohf_omp, OMP_NUM_THREADS={nthreads}), three-cylinder k-eps deck {nx}x{ny} "
+               f"({r[1]} active cells), one run of {nsteps} steps, the solver's own 'average speed' line"
+               + (f"; serial build on one core: {ser[0]:.4g} cell-updates/s" if ser else ""))
     else:
         cb = cpu_baseline_port()
-        v, how, ms = cb["value"], cb["sample"] + " (oracle/_ref not present: port used)", None
+        v, kind, cores, how, ms = cb["value"], "port", 1, cb["sample"] + " (oracle/_ref not present: oracle port used)", None
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "three cylinders, NS k-eps (9 equations), flat; bounded sample " + f"{nx}x{ny}", "per_step": per},
+            "config": {"workload": f"BASELINE configs[3]: three cylinders, NS k-eps URANS (9 equations), flat; bounded sample {nx}x{ny}, {nsteps} steps"},
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": how},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
+
+
+def stage2_bytes_per_cell(model, axi=False):
+    """Algorithmic bytes per cell of ONE k_stage2 launch (kernels): every plane the kernel owns read once and
+    written once, neighbour reads served on chip.  reads S, SN [Neq each], U,V,Tg,CP,R,k,p [+ mu, mu_t, lam, l_min if NS];
+    writes beta, S, A, B [Neq each], U,V,Tg,R,CP,k,p [+ mu, lam, mu_t if NS] [+ Src(Neq-7)] [+ F(Neq) if axisymmetric]."""
+    neq = {"keps": 9, "sa": 8}.get(model, 7)
+    ns = model != "euler"
+    r = 2 * neq + 7 + (4 if ns else 0)
+    w = 4 * neq + 7 + (3 if ns else 0) + (neq - 7) + (neq if axi else 0)
+    return 8.0 * (r + w)
+
+
+def cpu_baseline(model):
+    """CPU baseline beside the GPU number: the UNMODIFIED reference (oracle/_ref/ohf_serial, one core -- its OpenMP
+    build does not scale) on a bounded sample; the oracle port when the reference binary is absent."""
+    if model == "keps":
+        r = run_reference_binary("ohf_serial", 512, 256, 60, 1)
+        if r is not None:
+            return {"value": r[0], "unit": UNIT, "cores": 1, "kind": "reference",
+                    "sample": f"unmodified reference, serial build (oracle/_ref/ohf_serial), three-cylinder k-eps deck 512x256 "
+                              f"({r[1]} active cells), 60 steps, the solver's own 'average speed' line ({r[2]:.3g} step/s)"}
+    return cpu_baseline_port(model)
 
 
 def main():
@@ -187,6 +225,8 @@ def main():
     ap.add_argument("--nx", type=int, default=NX_PER_GPU)
     ap.add_argument("--ny", type=int, default=NY)
     ap.add_argument("--model", default="keps")
+    ap.add_argument("--seams", default="exact", choices=["exact", "lagged-chain"])
+    ap.add_argument("--rms-every", type=int, default=100, help="NOutStep: residual norms reduced every n-th step and on the last one")
     ap.add_argument("--e2e-steps", type=int, default=100)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
@@ -206,30 +246,48 @@ def main():
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    runner = SlabRunner(args.nx, args.ny, model=args.model, rank=rank, world=world, device=local)
+    runner = SlabRunner(args.nx, args.ny, model=args.model, rank=rank, world=world, device=local, seams=args.seams, rms_every=args.rms_every)
     act_local, tot_local = runner.active_cells()
     W, K = max(args.warmup, 3), args.steps
     runner.step(W)
     runner.barrier()
+    runner.solver.set_timing(True)          # event pairs around the two plain-tile launches, inside the timed region
     with ClockSampler(local) as cs:
         ms = runner.timed_steps(K)          # device time (CUDA events on the solver's stream), max over ranks
     clocks = cs.summary()
+    kt = runner.solver.get_timing()
+    runner.solver.set_timing(False)
     act = runner.allreduce_sum(act_local)
     value = act * K / (ms * 1e-3)
-    bpc = runner.solver.bytes_per_cell()
+    bpc_step = runner.solver.bytes_per_cell()
+    n_plain, n_gen, tc, tr = runner.solver.tile_counts()
+    plain_cells = n_plain * tc * tr
     peak, peak_src = peaks()
-    achieved = bpc * act_local * K / (ms * 1e-3) / 1e9
+    b2 = stage2_bytes_per_cell(args.model)
+    t2 = kt["stage2_plain_ms"] * 1e-3
+    achieved = b2 * plain_cells / t2 / 1e9 if t2 > 0 else 0.0
+    traffic = None
+    try:   # DRAM bytes per plain cell of one k_stage2 launch, from the committed ncu capture (profiles/)
+        with open(os.path.join(ROOT, "profiles", "stage2_traffic.json")) as f:
+            traffic = json.load(f).get(args.model, {}).get("dram_bytes_per_plain_cell") * plain_cells
+    except Exception:
+        pass
+    step_gbs = bpc_step * act_local * K / (ms * 1e-3) / 1e9
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"three cylinders, NS k-eps URANS (9 equations), flat, {args.nx}x{args.ny} cells per GPU "
+            "config": {"workload": f"BASELINE configs[3]: three cylinders, NS k-eps URANS (9 equations), flat, {args.nx}x{args.ny} cells per GPU "
                                    f"({args.nx * world}x{args.ny} total), X-slabs", "model": args.model,
-                       "active_cells": act, "total_cells": args.nx * args.ny * world,
-                       "l2": "working set per step (~7 GB/GPU) exceeds the 126 MB L2; no flush needed", "parallelism": f"x-slab{world}"},
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                         "bytes_per_cell": bpc, "peak_source": peak_src, "kernel": "k_stage1 + k_stage2 (whole step)"},
+                       "active_cells": act, "total_cells": args.nx * args.ny * world, "seams": args.seams, "rms_every": args.rms_every,
+                       "tiles_per_gpu": {"plain": n_plain, "general": n_gen, "cols": tc, "rows": tr},
+                       "l2": "per-step working set (~6 GB/GPU) >> 126 MB L2: no flush needed", "parallelism": f"x-slab{world}"},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                         "kernel": "k_stage2<plain tiles>", "bytes_per_cell": b2, "cells_per_launch": plain_cells,
+                         "kernel_ms": kt["stage2_plain_ms"], "kernel_launches_timed": kt["launches"][1], "peak_source": peak_src,
+                         "stage1_plain_ms": kt["stage1_plain_ms"],
+                         "whole_step": {"bytes_per_active_cell": bpc_step, "achieved": step_gbs, "frac": step_gbs / peak}},
             "gpu_launches": int(runner.launches_last), "clocks": clocks}
     if rank == 0 and not args.no_cpu:
-        line["cpu_baseline"] = cpu_baseline_port(args.model)
+        line["cpu_baseline"] = cpu_baseline(args.model)
     if not args.no_e2e:
         e2e = runner.e2e_cycle(args.e2e_steps)
         line["e2e"] = e2e

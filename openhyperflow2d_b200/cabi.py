@@ -63,7 +63,7 @@ EXPORTS = ["hf2d_gpu_last_error", "hf2d_gpu_device_count", "hf2d_gpu_create", "h
            "hf2d_gpu_download_aos", "hf2d_gpu_step", "hf2d_gpu_run_cycle", "hf2d_gpu_field_ptr", "hf2d_gpu_active_cells",
            "hf2d_gpu_bytes_per_cell", "hf2d_gpu_tile_counts", "hf2d_gpu_halo_bytes", "hf2d_gpu_halo_pack", "hf2d_gpu_halo_unpack", "hf2d_gpu_step_begin",
            "hf2d_gpu_step_prepass", "hf2d_gpu_step_stage1", "hf2d_gpu_step_stage2", "hf2d_gpu_step_end", "hf2d_gpu_dt_ptr", "hf2d_gpu_stream",
-           "hf2d_gpu_set_stream", "hf2d_gpu_dt_export", "hf2d_gpu_dt_import", "hf2d_gpu_launch_count"]
+           "hf2d_gpu_set_stream", "hf2d_gpu_set_timing", "hf2d_gpu_get_timing", "hf2d_gpu_dt_export", "hf2d_gpu_dt_import", "hf2d_gpu_launch_count"]
 
 
 def lib():
@@ -95,6 +95,8 @@ def lib():
         L.hf2d_gpu_set_stream.argtypes = [C.c_void_p, C.c_void_p]
         L.hf2d_gpu_dt_export.argtypes = [C.c_void_p, C.c_void_p]
         L.hf2d_gpu_dt_import.argtypes = [C.c_void_p, C.c_void_p]
+        L.hf2d_gpu_set_timing.argtypes = [C.c_void_p, C.c_int]
+        L.hf2d_gpu_get_timing.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int)]
         L.hf2d_gpu_launch_count.argtypes = [C.c_void_p]
         L.hf2d_gpu_launch_count.restype = C.c_ulonglong
         _lib = L
@@ -245,6 +247,14 @@ class Solver:
 
     def dt_import(self, dev_ptr: int):
         _ck(lib().hf2d_gpu_dt_import(self._h, C.c_void_p(dev_ptr)))
+
+    def set_timing(self, enable=True):
+        _ck(lib().hf2d_gpu_set_timing(self._h, int(enable)))
+
+    def get_timing(self):
+        ms, cnt = (C.c_double * 2)(), (C.c_int * 2)()
+        _ck(lib().hf2d_gpu_get_timing(self._h, ms, cnt))
+        return {"stage1_plain_ms": ms[0], "stage2_plain_ms": ms[1], "launches": (cnt[0], cnt[1])}
 
     def launch_count(self) -> int:
         return int(lib().hf2d_gpu_launch_count(self._h))

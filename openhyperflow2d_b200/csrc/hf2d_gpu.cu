@@ -55,6 +55,8 @@ struct hf2d_gpu {
     int TI, n_sb, n_tx;
     int *d_tiles_plain, *d_tiles_gen; int n_plain, n_gen;
     int plain_ttc;                  // TurbType word of the plain tiles (-1: no plain kernel for this grid)
+    // optional per-kernel timing of the two plain-tile launches (bench.py roofline): event pairs on the main stream
+    bool timing; std::vector<cudaEvent_t> tev[2][2]; int tn[2];
     bool prepass_done;              // hf2d_gpu_step_prepass already ran for the current step
     int rms_every;                  // residual norms are reduced on steps with iter % rms_every == 0 and on the last step of a call
 };
@@ -119,7 +121,7 @@ extern "C" int hf2d_gpu_create(const hf2d_cfg* cfg, int device, hf2d_gpu** out) 
     P.pow_cmu_34[0] = pow(0.09, 3. / 4.); P.pow_cmu_34[1] = pow(0.0845, 3. / 4.);
     P.tab = h->d_tab; P.st = h->d_st;
     h->last_iter_cycle = cfg->last_iter;
-    h->rms_every = cfg->NOutStep; h->prepass_done = false;
+    h->rms_every = cfg->NOutStep; h->prepass_done = false; h->timing = false; h->tn[0] = h->tn[1] = 0;
     h->TI = 16; h->n_sb = h->n_tx = 0; h->d_tiles_plain = h->d_tiles_gen = nullptr; h->n_plain = h->n_gen = 0; h->plain_ttc = -1;
     *out = h;
     return HF2D_OK;
@@ -133,6 +135,7 @@ extern "C" int hf2d_gpu_destroy(hf2d_gpu* h) {
     if (h->d_stage) cudaFree(h->d_stage);
     if (h->h_st) cudaFreeHost(h->h_st);
     cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
+    for (int a = 0; a < 2; a++) for (int b = 0; b < 2; b++) for (cudaEvent_t e : h->tev[a][b]) cudaEventDestroy(e);
     cudaStreamDestroy(h->stream0); cudaStreamDestroy(h->stream_b); cudaEventDestroy(h->ev_fork); cudaEventDestroy(h->ev_join);
     delete h;
     return HF2D_OK;
