@@ -114,6 +114,10 @@ int  hf2d_gpu_download_aos(hf2d_gpu* h, void* J, const hf2d_node_layout* layout,
  * isSrcAdd evaluated once at cycle start, deeps2d_core.cpp:727-731).  Asynchronous on the handle's stream
  * until the report is read at the end.  `want_rms` = 0 skips the residual reduction read-back. */
 int  hf2d_gpu_step(hf2d_gpu* h, int nsteps, hf2d_step_report* report);
+/* further steps of the SAME cycle (isSrcAdd and time_part carry on): lets a shim report every NOutStep steps (:1602-1637) */
+int  hf2d_gpu_step_continue(hf2d_gpu* h, int nsteps, hf2d_step_report* report);
+/* p and Tg of one node (monitor points, :1576-1600) */
+int  hf2d_gpu_read_node(hf2d_gpu* h, int i, int j, double* p, double* Tg);
 
 /* One reference output cycle through host memory: upload + nsteps + download (what a shim that keeps J on the
  * host between cycles does).  Used for the end-to-end metric. */

@@ -1,0 +1,235 @@
+// deeps2d_run_gpu.cpp -- the reference-side shim: DEEPS2D_Run (libDEEPS2D/deeps2d_core.cpp:512-2023) with its inner
+// time loop (:735-1642) replaced by libhf2d_gpu.so (include/hf2d_gpu.h).
+//
+// Build (oracle/Makefile, target `shim`): the reference's deeps2d_core.cpp is compiled with
+// -DDEEPS2D_Run=DEEPS2D_Run_cpu, every other reference source as is, and this file supplies DEEPS2D_Run.  The result
+// (oracle/_ref/ohf_gpu) is the reference program -- its own main(), input-deck parser, InitDEEPS2D, geometry
+// rasterisers, Tecplot/RMS/monitor writers, swap-file sync and exit path -- running its time steps on the GPU.
+// This file includes the reference's headers and is compiled only where the reference tree is present; nothing of
+// the reference is copied here.  What stays on the host is exactly what the reference does once per output cycle or
+// every NOutStep steps; the per-cell work is behind the C ABI.
+#include "libDEEPS2D/deeps2d_core.hpp"
+#include "hf2d_gpu.h"
+#include <sys/time.h>
+#include <unistd.h>
+#include <cstddef>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+typedef FlowNode2D<FP, NUM_COMPONENTS> Node;
+
+// file-scope globals of deeps2d_core.cpp that its header does not export (deeps2d_core.cpp:20-158)
+extern FP dt, beta0, CFL, nrbc_beta0, SigW, SigF, GlobalTime, CurrentTimePart, ExitMonitorValue, Ts0;
+extern Table *CFL_Scenario, *beta_Scenario;
+extern BlendingFactorFunction bFF;
+extern int TurbStartIter, TurbExtModel, isTurbulenceReset, isAdiabaticWall, isAlternateRMS;
+extern int Nstep, NOutStep, NSaveStep, I, MonitorIndex, MonitorCondition, isRun, turb_mod_name_index;
+extern unsigned int AddSrcStartIter, last_iter;
+extern UArray<XCut>* XCutArray;
+extern int is_Cx_calc, Cx_Flow_index, Cp_Flow_index, y_max, y_min, isOutHeatFluxX, isOutHeatFluxY;
+extern FP x0_body, y0_body, dx_body, dy_body;
+extern const char* RMS_Name[11];
+extern char RMSFileName[255], MonitorsFileName[255], ErrFileName[255], TecPlotFileName[255];
+extern ofstream *pRMS_OutFile, *pMonitors_OutFile, *pHeatFlux_OutFile;
+extern UArray<Flow2D*>* Flow2DList;
+
+static void die(ofstream* f, const char* what) {
+    *f << "\nhf2d_gpu: " << what << ": " << hf2d_gpu_last_error() << "\n" << flush;
+    Abort_OpenHyperFLOW2D();
+}
+
+static void set_table(hf2d_table* t, Table* src) {
+    if (src == NULL || src == InputData::GetZeroTable() || src->n == 0) { t->n = 0; t->x = t->y = NULL; return; }
+    t->n = (int)src->n;
+    double* x = new double[src->n]; double* y = new double[src->n];
+    for (unsigned i = 0; i < src->n; i++) { x[i] = src->x[i]; y[i] = src->y[i]; }
+    t->x = x; t->y = y;
+}
+
+#define OFFS(m) L.m = (size_t)((char*)&(n0->m) - (char*)n0)
+static hf2d_node_layout node_layout() {
+    hf2d_node_layout L; memset(&L, 0, sizeof(L));
+    Node* n0 = (Node*)malloc(sizeof(Node));
+    L.node_bytes = sizeof(Node);
+    L.S = (size_t)((char*)&(n0->S[0]) - (char*)n0); L.dSdx = (size_t)((char*)&(n0->dSdx[0]) - (char*)n0); L.dSdy = (size_t)((char*)&(n0->dSdy[0]) - (char*)n0);
+    OFFS(TurbType); OFFS(l_min); OFFS(y_plus); OFFS(mu_t); OFFS(lam_t); OFFS(dkdx); OFFS(dkdy); OFFS(depsdx); OFFS(depsdy); OFFS(y); OFFS(p);
+    OFFS(idXl); OFFS(idYu); OFFS(idXr); OFFS(idYd); OFFS(CT);
+    L.beta = (size_t)((char*)&(n0->beta[0]) - (char*)n0);
+    OFFS(Q_conv); OFFS(time); OFFS(k); OFFS(R); OFFS(lam); OFFS(mu); OFFS(CP); OFFS(Diff); OFFS(Tf);
+    L.A = (size_t)((char*)&(n0->A[0]) - (char*)n0); L.B = (size_t)((char*)&(n0->B[0]) - (char*)n0); L.F = (size_t)((char*)&(n0->F[0]) - (char*)n0);
+    L.Src = (size_t)((char*)&(n0->Src[0]) - (char*)n0); L.SrcAdd = (size_t)((char*)&(n0->SrcAdd[0]) - (char*)n0);
+    OFFS(Tg); OFFS(U); OFFS(V);
+    L.Y = (size_t)((char*)&(n0->Y[0]) - (char*)n0);
+    OFFS(Uw); OFFS(Vw);
+    L.droYdx = (size_t)((char*)&(n0->droYdx[0]) - (char*)n0); L.droYdy = (size_t)((char*)&(n0->droYdy[0]) - (char*)n0);
+    OFFS(dUdx); OFFS(dUdy); OFFS(dVdx); OFFS(dVdy); OFFS(dTdx); OFFS(dTdy); OFFS(BGX); OFFS(BGY);
+    free(n0);
+    return L;
+}
+
+static void fill_cfg(hf2d_cfg* c) {
+    memset(c, 0, sizeof(*c));
+    ChemicalReactionsModelData2D* ch = &chemical_reactions;
+    c->nx = (int)MaxX; c->ny = (int)MaxY; c->dx = dx; c->dy = dy; c->dt = dt;
+    c->CFL = CFL; c->beta0 = beta0; c->nrbc_beta0 = nrbc_beta0; c->bFF = (int)bFF;
+    c->problem_type = (int)ProblemType; c->flow_type = (int)Node::FT;
+    for (int q = 0; q < 4; q++) c->Hu[q] = Node::Hu[q];
+    c->TurbStartIter = TurbStartIter; c->TurbExtModel = TurbExtModel; c->isTurbulenceReset = isTurbulenceReset;
+    c->SigW = SigW; c->SigF = SigF; c->delta_bl = delta_bl;
+    c->turb_intensity = 0.005;   // FlowNodeTurbulence2D::I: private static, in-class default, never set (hyper_flow_turbulence.hpp:133)
+    c->isAdiabaticWall = isAdiabaticWall; c->isAlternateRMS = isAlternateRMS;
+    c->AddSrcStartIter = AddSrcStartIter; c->last_iter = last_iter;
+    c->MonitorIndex = MonitorIndex; c->ExitMonitorValue = ExitMonitorValue;
+    c->K0 = ch->K0; c->Rgas[0] = ch->R_Fuel; c->Rgas[1] = ch->R_OX; c->Rgas[2] = ch->R_cp; c->Rgas[3] = ch->R_air;
+    Table* tabs[HF2D_NTABLES] = {ch->Cp_Fuel, ch->Cp_OX, ch->Cp_cp, ch->Cp_air, ch->lam_Fuel, ch->lam_OX, ch->lam_cp, ch->lam_air,
+                                 ch->mu_Fuel, ch->mu_OX, ch->mu_cp, ch->mu_air, CFL_Scenario, beta_Scenario};
+    for (int t = 0; t < HF2D_NTABLES; t++) set_table(&c->tab[t], tabs[t]);
+    c->dt_rule = 0;              // the serial build's running minimum (deeps2d_core.cpp:803, 1326)
+    c->rank = 0; c->n_ranks = 1;
+    c->NOutStep = NOutStep;
+}
+
+void DEEPS2D_Run(ofstream* f_stream) {
+    struct timeval start, stop, mark1, mark2;
+    // --- files (deeps2d_core.cpp:663-672) ---
+    snprintf(RMSFileName, 255, "RMS-%s", OutFileName);
+    CutFile(RMSFileName);
+    pRMS_OutFile = OpenData(RMSFileName);
+    SaveRMSHeader(pRMS_OutFile);
+    if (MonitorPointsArray && MonitorPointsArray->GetNumElements() > 0) {
+        snprintf(MonitorsFileName, 255, "Monitors-%s", OutFileName);
+        CutFile(MonitorsFileName);
+        pMonitors_OutFile = OpenData(MonitorsFileName);
+        SaveMonitorsHeader(pMonitors_OutFile, MonitorPointsArray);
+    }
+    // --- the grid goes to the GPU once; it comes back before every per-cycle writer runs ---
+    hf2d_cfg cfg; fill_cfg(&cfg);
+    const hf2d_node_layout lay = node_layout();
+    hf2d_gpu* h = NULL;
+    const char* dev = getenv("HF2D_DEVICE");
+    if (hf2d_gpu_create(&cfg, dev ? atoi(dev) : 0, &h)) die(f_stream, "create");
+    if (hf2d_gpu_upload_aos(h, J->GetMatrixPtr(), &lay, 0)) die(f_stream, "upload");
+    *f_stream << "hf2d_gpu: DEEPS2D time loop on the GPU (" << MaxX << "x" << MaxY << " nodes)\n" << flush;
+
+    I = 0; isRun = 1;
+    FP max_RMS = 0.; int k_max_RMS = -1;
+    do {
+        gettimeofday(&mark2, NULL);
+        gettimeofday(&start, NULL);
+        // one output cycle = Nstep steps; the reference looks at the residuals on steps with iter % NOutStep == 0
+        hf2d_step_report rep; memset(&rep, 0, sizeof(rep));
+        int done = 0;
+        while (done < Nstep) {
+            // the step with in-cycle index `done` is an output step iff done % NOutStep == 0: run up to and including it
+            int n = (done % NOutStep == 0) ? 1 : (NOutStep - done % NOutStep);
+            if (done + n > Nstep) n = Nstep - done;
+            const int rc = done == 0 ? hf2d_gpu_step(h, n, &rep) : hf2d_gpu_step_continue(h, n, &rep);
+            if (rc == HF2D_EUNSTABLE) {               // Tg < 0 (deeps2d_core.cpp:1246-1316): error snapshot + abort
+                hf2d_gpu_download_aos(h, J->GetMatrixPtr(), &lay, 0);
+                *f_stream << "\nTg=" << J->GetValue(rep.err_i, rep.err_j).Tg << " K. p=" << J->GetValue(rep.err_i, rep.err_j).p
+                          << " Pa dt=" << rep.dt << " sec.\nComputational unstability in node (" << rep.err_i << "," << rep.err_j << ") on iteration "
+                          << rep.iter << "\n" << flush;
+                DataSnapshot(ErrFileName);
+                Abort_OpenHyperFLOW2D();
+            } else if (rc) die(f_stream, "step");
+            done += n;
+            iter = (unsigned)done;
+            dt = rep.dt;
+            CurrentTimePart = rep.time_part;
+            const unsigned it_last = (unsigned)(done - 1);          // in-cycle index of the step just finished
+            max_RMS = rep.max_RMS; k_max_RMS = rep.k_max_RMS;
+            if (it_last % (unsigned)NOutStep == 0) {                  // deeps2d_core.cpp:1576-1637
+                if (MonitorPointsArray) {
+                    for (int m = 0; m < (int)MonitorPointsArray->GetNumElements(); m++) {
+                        MonitorPoint& mp = MonitorPointsArray->GetElement(m);
+                        double pp = 0., tt = 0.;
+                        hf2d_gpu_read_node(h, (int)(mp.MonitorXY.GetX() / dx), (int)(mp.MonitorXY.GetY() / dy), &pp, &tt);
+                        mp.p = pp; mp.T = tt;
+                    }
+                }
+                if (isVerboseOutput) {
+                    gettimeofday(&mark1, NULL);
+                    const FP d_time = (FP)(mark1.tv_sec - mark2.tv_sec) + (FP)(mark1.tv_usec - mark2.tv_usec) * 1.e-6;
+                    const FP VCOMP = d_time > 0. ? (FP)(NOutStep) / d_time : 0.;
+                    memcpy(&mark2, &mark1, sizeof(mark1));
+                    FP rms[HF2D_NEQ];
+                    for (int k = 0; k < HF2D_NEQ; k++) rms[k] = rep.sum_RMS[k];
+                    SaveRMS(pRMS_OutFile, last_iter + it_last, rms);
+                    if (MonitorPointsArray && MonitorPointsArray->GetNumElements() > 0)
+                        SaveMonitors(pMonitors_OutFile, GlobalTime + CurrentTimePart, MonitorPointsArray);
+                    int kk = k_max_RMS;
+                    if (kk == i2d_nu_t) kk += turb_mod_name_index;
+                    if (kk != -1 && (MonitorIndex == 0 || MonitorIndex == 5))
+                        *f_stream << "Step No " << it_last + last_iter << " maxRMS[" << RMS_Name[kk] << "]=" << (FP)(max_RMS * 100.)
+                                  << " % step_time=" << (FP)d_time << " sec (" << (FP)VCOMP << " step/sec) dt=" << dt << "\n" << flush;
+                    else if (MonitorIndex > 0 && MonitorIndex < 5)
+                        *f_stream << "Step No " << it_last + last_iter << " maxRMS[" << RMS_Name[MonitorIndex - 1] << "]=" << (FP)(max_RMS * 100.)
+                                  << " % step_time=" << (FP)d_time << " sec (" << (FP)VCOMP << " step/sec) dt=" << dt << "\n" << flush;
+                    else
+                        *f_stream << "Step No " << it_last + last_iter << " maxRMS[" << kk << "]=" << (FP)(max_RMS * 100.)
+                                  << " % step_time=" << (FP)d_time << " sec (" << (FP)VCOMP << " step/sec) dt=" << dt << "\n" << flush;
+                }
+            }
+        }
+        // --- cycle end (deeps2d_core.cpp:1762-1849): grid back to the host image, then the reference's own writers ---
+        if (hf2d_gpu_download_aos(h, J->GetMatrixPtr(), &lay, 0)) die(f_stream, "download");
+        if (XCutArray->GetNumElements() > 0) {
+            for (int i_xcut = 0; i_xcut < (int)XCutArray->GetNumElements(); i_xcut++) {
+                XCut* c = XCutArray->GetElementPtr(i_xcut);
+                *f_stream << "Cut(" << i_xcut + 1 << ") X=" << c->x0 << " Y=" << c->y0 << " dY=" << c->dy << " MassFlow="
+                          << CalcMassFlowRateX2D(J, c->x0, c->y0, c->dy) << "  (kg/sec*m)" << endl;
+            }
+        }
+        gettimeofday(&stop, NULL);
+        *f_stream << "\nSave current results in file " << OutFileName << "...\n" << flush;
+        DataSnapshot(OutFileName, WM_REWRITE);
+        if ((I / NSaveStep) * NSaveStep == I) {
+            *f_stream << "Add current results to transient solution file " << TecPlotFileName << "...\n" << flush;
+            DataSnapshot(TecPlotFileName, WM_APPEND);
+        }
+        I++;
+        const FP c_time = (FP)(stop.tv_sec - start.tv_sec) + (FP)(stop.tv_usec - start.tv_usec) * 1.e-6;
+        *f_stream << "HyperFLOW/DEEPS computation cycle time=" << (FP)c_time << " sec ( average  speed " << (FP)(Nstep / c_time) << " step/sec).       \n" << flush;
+        last_iter += iter;
+        iter = 0;
+        GlobalTime += CurrentTimePart;
+        CurrentTimePart = 0.;
+        if (isOutHeatFluxX) {
+            char fn[255]; snprintf(fn, 255, "HeatFlux-X-%s", OutFileName); CutFile(fn);
+            pHeatFlux_OutFile = OpenData(fn);
+            SaveXHeatFlux2D(pHeatFlux_OutFile, J, Flow2DList->GetElement(Cp_Flow_index - 1), Ts0, y_max, y_min);
+            pHeatFlux_OutFile->close();
+        }
+        if (isOutHeatFluxY) {
+            char fn[255]; snprintf(fn, 255, "HeatFlux-Y-%s", OutFileName); CutFile(fn);
+            pHeatFlux_OutFile = OpenData(fn);
+            SaveYHeatFlux2D(pHeatFlux_OutFile, J, Ts0);
+            pHeatFlux_OutFile->close();
+        }
+        if (is_Cx_calc)
+            *f_stream << "\nCx = " << Calc_Cx_2D(J, x0_body, y0_body, dx_body, dy_body, Flow2DList->GetElement(Cx_Flow_index - 1))
+                      << " Cy = " << Calc_Cy_2D(J, x0_body, y0_body, dx_body, dy_body, Flow2DList->GetElement(Cx_Flow_index - 1))
+                      << " Fx = " << CalcXForce2D(J, x0_body, y0_body, dx_body, dy_body) << " Fy = " << CalcYForce2D(J, x0_body, y0_body, dx_body, dy_body) << endl;
+        if (GasSwapData) {                                   // swap-file sync (_NO_MMAP_ build): rewrite the raw AoS image
+            if (isVerboseOutput) *f_stream << "\nSync swap file for gas..." << flush;
+            const char* ptr = (const char*)J->GetMatrixPtr();
+            const size_t total = (size_t)J->GetMatrixSize();
+            size_t len = 0;
+            while (len < total) {
+                const size_t one = (total - len > ((size_t)1 << 30)) ? ((size_t)1 << 30) : total - len;
+                const ssize_t w = pwrite(fd_g, ptr + len, one, (off_t)len);
+                if (w <= 0) break;
+                len += (size_t)w;
+            }
+            if (len != total) *f_stream << "Error: len(" << len << ") != FileSize(" << total << ") " << endl << flush;
+            *f_stream << "OK" << endl;
+        }
+        if (MonitorIndex < 5) MonitorCondition = (max_RMS > ExitMonitorValue) ? 1 : 0;
+        else MonitorCondition = (GlobalTime < ExitMonitorValue) ? 1 : 0;
+    } while (MonitorCondition);
+    DataSnapshot(OutFileName, WM_REWRITE);
+    hf2d_gpu_destroy(h);
+    *f_stream << "\nReady. Computation finished.\n" << flush;
+    Exit_OpenHyperFLOW2D();
+}
