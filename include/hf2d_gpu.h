@@ -109,6 +109,11 @@ int  hf2d_gpu_destroy(hf2d_gpu* h);
 int  hf2d_gpu_upload_aos(hf2d_gpu* h, const void* J, const hf2d_node_layout* layout, int pinned);
 /* SoA arrays -> host AoS image; only members the step owns are written, everything else in J is left alone. */
 int  hf2d_gpu_download_aos(hf2d_gpu* h, void* J, const hf2d_node_layout* layout, int pinned);
+/* Page-lock / release the caller's grid image (cudaHostRegister) so that the upload and the per-cycle downloads run
+ * at PCIe speed; worth it when J lives through many output cycles (the reference allocates it once, hf2d_start.cpp:60-146).
+ * Optional: pageable memory works, slower. */
+int  hf2d_gpu_pin_host(void* J, size_t bytes);
+int  hf2d_gpu_unpin_host(void* J);
 
 /* `nsteps` explicit time steps (one output cycle of the reference: iter = 0..nsteps-1 with last_iter fixed,
  * isSrcAdd evaluated once at cycle start, deeps2d_core.cpp:727-731).  Asynchronous on the handle's stream

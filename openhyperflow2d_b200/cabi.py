@@ -60,7 +60,7 @@ class Hf2dError(RuntimeError):
 
 _lib = None
 EXPORTS = ["hf2d_gpu_last_error", "hf2d_gpu_device_count", "hf2d_gpu_create", "hf2d_gpu_destroy", "hf2d_gpu_upload_aos",
-           "hf2d_gpu_download_aos", "hf2d_gpu_step", "hf2d_gpu_step_continue", "hf2d_gpu_read_node", "hf2d_gpu_run_cycle", "hf2d_gpu_field_ptr", "hf2d_gpu_active_cells",
+           "hf2d_gpu_download_aos", "hf2d_gpu_pin_host", "hf2d_gpu_unpin_host", "hf2d_gpu_step", "hf2d_gpu_step_continue", "hf2d_gpu_read_node", "hf2d_gpu_run_cycle", "hf2d_gpu_field_ptr", "hf2d_gpu_active_cells",
            "hf2d_gpu_bytes_per_cell", "hf2d_gpu_tile_counts", "hf2d_gpu_halo_bytes", "hf2d_gpu_halo_pack", "hf2d_gpu_halo_unpack", "hf2d_gpu_step_begin",
            "hf2d_gpu_step_prepass", "hf2d_gpu_step_stage1", "hf2d_gpu_step_stage2", "hf2d_gpu_step_end", "hf2d_gpu_dt_ptr", "hf2d_gpu_stream",
            "hf2d_gpu_set_stream", "hf2d_gpu_set_timing", "hf2d_gpu_get_timing", "hf2d_gpu_dt_export", "hf2d_gpu_dt_import", "hf2d_gpu_launch_count"]
@@ -76,6 +76,8 @@ def lib():
         L.hf2d_gpu_destroy.argtypes = [C.c_void_p]
         L.hf2d_gpu_upload_aos.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(NodeLayout), C.c_int]
         L.hf2d_gpu_download_aos.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(NodeLayout), C.c_int]
+        L.hf2d_gpu_pin_host.argtypes = [C.c_void_p, C.c_size_t]
+        L.hf2d_gpu_unpin_host.argtypes = [C.c_void_p]
         L.hf2d_gpu_step.argtypes = [C.c_void_p, C.c_int, C.POINTER(StepReport)]
         L.hf2d_gpu_step_continue.argtypes = [C.c_void_p, C.c_int, C.POINTER(StepReport)]
         L.hf2d_gpu_read_node.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]

@@ -50,6 +50,7 @@ struct hf2d_gpu {
     unsigned last_iter_cycle;       // last_iter of the reference (fixed during one cycle)
     uint64_t launches;
     void* d_stage; size_t stage_bytes;
+    void* d_image; size_t image_bytes;   // the raw record image, resident when it fits (hf2d_io.inc)
     double bytes_per_cell;
     // strip-sweep tiles (hf2d_stage2.cuh): TI columns x S2_WARPS strips of STRIP_ROWS rows
     int TI, n_sb, n_tx;
@@ -84,7 +85,7 @@ extern "C" int hf2d_gpu_create(const hf2d_cfg* cfg, int device, hf2d_gpu** out) 
     if (device < 0 || device >= ndev) return fail(HF2D_EINVAL, "device %d out of range (%d devices)", device, ndev);
     CK(cudaSetDevice(device));
     hf2d_gpu* h = new hf2d_gpu();
-    h->cfg = *cfg; h->device = device; h->uploaded = false; h->launches = 0; h->d_stage = nullptr; h->stage_bytes = 0;
+    h->cfg = *cfg; h->device = device; h->uploaded = false; h->launches = 0; h->d_stage = nullptr; h->stage_bytes = 0; h->d_image = nullptr; h->image_bytes = 0;
     h->d_nlist = h->d_wall_list = nullptr; h->n_nlist = h->n_wall = 0; h->n_active = 0;
     for (int t = 0; t < HF2D_NTABLES; t++) { h->cfg.tab[t].x = nullptr; h->cfg.tab[t].y = nullptr; }
     CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
@@ -133,6 +134,7 @@ extern "C" int hf2d_gpu_destroy(hf2d_gpu* h) {
     cudaStreamSynchronize(h->stream);
     for (void* p : h->allocs) cudaFree(p);
     if (h->d_stage) cudaFree(h->d_stage);
+    if (h->d_image) cudaFree(h->d_image);
     if (h->h_st) cudaFreeHost(h->h_st);
     cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
     for (int a = 0; a < 2; a++) for (int b = 0; b < 2; b++) for (cudaEvent_t e : h->tev[a][b]) cudaEventDestroy(e);

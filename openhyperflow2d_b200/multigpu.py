@@ -189,9 +189,9 @@ class SlabRunner(SlabProtocol):
             torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
             el = float(t.item())
         tot = self.allreduce_sum(act)
-        return {"value": tot * nsteps / el, "unit": "cell-updates/s", "h2d_bytes_per_step": int(self.J.nbytes * 2 / nsteps),
+        return {"value": tot * nsteps / el, "unit": "cell-updates/s", "h2d_bytes_per_step": int(self.J.nbytes / nsteps),
                 "d2h_bytes_per_step": int(self.J.nbytes / nsteps), "steps_per_cycle": nsteps, "seconds": el,
-                "note": "hf2d_gpu_run_cycle: pinned host AoS -> HBM SoA, nsteps steps, HBM -> host AoS (download re-reads the image: 2x H2D)"}
+                "note": "hf2d_gpu_run_cycle: pinned host AoS image -> HBM (scanned + unpacked there), nsteps steps, packed into the resident image -> host"}
 
     def close(self):
         self.solver.close()

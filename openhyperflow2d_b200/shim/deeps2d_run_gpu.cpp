@@ -109,7 +109,9 @@ void DEEPS2D_Run(ofstream* f_stream) {
     hf2d_gpu* h = NULL;
     const char* dev = getenv("HF2D_DEVICE");
     if (hf2d_gpu_create(&cfg, dev ? atoi(dev) : 0, &h)) die(f_stream, "create");
-    if (hf2d_gpu_upload_aos(h, J->GetMatrixPtr(), &lay, 0)) die(f_stream, "upload");
+    // J lives as long as the run: page-lock it once so every per-cycle download runs at PCIe speed (optional)
+    const int pinned = hf2d_gpu_pin_host(J->GetMatrixPtr(), (size_t)J->GetMatrixSize()) == 0;
+    if (hf2d_gpu_upload_aos(h, J->GetMatrixPtr(), &lay, pinned)) die(f_stream, "upload");
     *f_stream << "hf2d_gpu: DEEPS2D time loop on the GPU (" << MaxX << "x" << MaxY << " nodes)\n" << flush;
 
     I = 0; isRun = 1;
@@ -126,7 +128,7 @@ void DEEPS2D_Run(ofstream* f_stream) {
             if (done + n > Nstep) n = Nstep - done;
             const int rc = done == 0 ? hf2d_gpu_step(h, n, &rep) : hf2d_gpu_step_continue(h, n, &rep);
             if (rc == HF2D_EUNSTABLE) {               // Tg < 0 (deeps2d_core.cpp:1246-1316): error snapshot + abort
-                hf2d_gpu_download_aos(h, J->GetMatrixPtr(), &lay, 0);
+                hf2d_gpu_download_aos(h, J->GetMatrixPtr(), &lay, pinned);
                 *f_stream << "\nTg=" << J->GetValue(rep.err_i, rep.err_j).Tg << " K. p=" << J->GetValue(rep.err_i, rep.err_j).p
                           << " Pa dt=" << rep.dt << " sec.\nComputational unstability in node (" << rep.err_i << "," << rep.err_j << ") on iteration "
                           << rep.iter << "\n" << flush;
@@ -173,7 +175,7 @@ void DEEPS2D_Run(ofstream* f_stream) {
             }
         }
         // --- cycle end (deeps2d_core.cpp:1762-1849): grid back to the host image, then the reference's own writers ---
-        if (hf2d_gpu_download_aos(h, J->GetMatrixPtr(), &lay, 0)) die(f_stream, "download");
+        if (hf2d_gpu_download_aos(h, J->GetMatrixPtr(), &lay, pinned)) die(f_stream, "download");
         if (XCutArray->GetNumElements() > 0) {
             for (int i_xcut = 0; i_xcut < (int)XCutArray->GetNumElements(); i_xcut++) {
                 XCut* c = XCutArray->GetElementPtr(i_xcut);
@@ -229,6 +231,7 @@ void DEEPS2D_Run(ofstream* f_stream) {
         else MonitorCondition = (GlobalTime < ExitMonitorValue) ? 1 : 0;
     } while (MonitorCondition);
     DataSnapshot(OutFileName, WM_REWRITE);
+    if (pinned) hf2d_gpu_unpin_host(J->GetMatrixPtr());
     hf2d_gpu_destroy(h);
     *f_stream << "\nReady. Computation finished.\n" << flush;
     Exit_OpenHyperFLOW2D();
