@@ -8,8 +8,10 @@ A "step" is one DEEPS2D time step (Stage 1 + Stage 2 + dt/RMS reductions + wall 
 Workload (config.workload): BASELINE configs[3], "hypersonic flow around three cylinders, k-eps URANS", weak scaling
 2048 x 4096 cells per GPU (16384 x 4096 at 8 GPUs), synthetic grid from openhyperflow2d_b200.gridgen.
 value  = active cells * K / device time (max over ranks), inputs resident in HBM.
-e2e    = same metric through the C ABI with HOST AoS buffers: hf2d_gpu_run_cycle = upload + n steps + download
-         (what a DEEPS2D_Run shim does once per output cycle), pinned host memory, copies inside the timed region.
+e2e    = same metric through the C ABI with HOST AoS buffers: hf2d_gpu_run_cycle = upload + Nmax steps + download
+         (one output cycle of a DEEPS2D_Run shim that keeps nothing on the GPU between cycles), pinned host memory,
+         copies inside the timed region.  Nmax = 500, the smallest value in the reference's own decks (TestCases/*.dat:
+         TriplePoint 500, ObliqueShock 12000, Wedge 15000, Step 24000).
 roofline.achieved = algorithmic bytes/cell * active cells / mean device time of one step.
 """
 from __future__ import annotations
@@ -227,7 +229,8 @@ def main():
     ap.add_argument("--model", default="keps")
     ap.add_argument("--seams", default="exact", choices=["exact", "lagged-chain"])
     ap.add_argument("--rms-every", type=int, default=100, help="NOutStep: residual norms reduced every n-th step and on the last one")
-    ap.add_argument("--e2e-steps", type=int, default=100)
+    ap.add_argument("--e2e-steps", type=int, default=500,
+                    help="steps per output cycle (Nmax) of the end-to-end leg; the reference's own decks use 500 (TriplePoint.dat) to 24000 (Step.dat)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()

@@ -191,7 +191,7 @@ class SlabRunner(SlabProtocol):
         tot = self.allreduce_sum(act)
         return {"value": tot * nsteps / el, "unit": "cell-updates/s", "h2d_bytes_per_step": int(self.J.nbytes / nsteps),
                 "d2h_bytes_per_step": int(self.J.nbytes / nsteps), "steps_per_cycle": nsteps, "seconds": el,
-                "note": "hf2d_gpu_run_cycle: pinned host AoS image -> HBM (scanned + unpacked there), nsteps steps, packed into the resident image -> host"}
+                "note": "hf2d_gpu_run_cycle: pinned host AoS image -> HBM (scanned + unpacked there), nsteps steps (= Nmax, one output cycle), packed into the resident image -> host"}
 
     def close(self):
         self.solver.close()
