@@ -228,6 +228,8 @@ def main():
     ap.add_argument("--ny", type=int, default=NY)
     ap.add_argument("--model", default="keps")
     ap.add_argument("--seams", default="exact", choices=["exact", "lagged-chain"])
+    ap.add_argument("--schedule", default="overlapped", choices=["overlapped", "sequential"],
+                    help="N>1: seam exchange on a side stream beside the bulk tiles, or everything in sequence on one stream")
     ap.add_argument("--rms-every", type=int, default=100, help="NOutStep: residual norms reduced every n-th step and on the last one")
     ap.add_argument("--e2e-steps", type=int, default=500,
                     help="steps per output cycle (Nmax) of the end-to-end leg; the reference's own decks use 500 (TriplePoint.dat) to 24000 (Step.dat)")
@@ -248,8 +250,9 @@ def main():
     torch.cuda.set_device(local)
     if world > 1:
         import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    runner = SlabRunner(args.nx, args.ny, model=args.model, rank=rank, world=world, device=local, seams=args.seams, rms_every=args.rms_every)
+        opts = dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)   # seam traffic must not queue behind the bulk kernels
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local), pg_options=opts)
+    runner = SlabRunner(args.nx, args.ny, model=args.model, rank=rank, world=world, device=local, seams=args.seams, rms_every=args.rms_every, schedule=args.schedule)
     act_local, tot_local = runner.active_cells()
     W, K = max(args.warmup, 3), args.steps
     runner.step(W)
@@ -260,10 +263,15 @@ def main():
     clocks = cs.summary()
     kt = runner.solver.get_timing()
     runner.solver.set_timing(False)
+    if os.environ.get("HF2D_BENCH_RANKS") == "1":   # per-rank view: tile mix and the two timed launches
+        print(f"[rank {rank}] tiles {runner.solver.tile_counts()} edge {runner.solver.edge_tile_counts()} active {act_local} "
+              f"s1_plain {kt['stage1_plain_ms']:.3f} ms  s2_plain {kt['stage2_plain_ms']:.3f} ms", file=sys.stderr, flush=True)
     act = runner.allreduce_sum(act_local)
     value = act * K / (ms * 1e-3)
     bpc_step = runner.solver.bytes_per_cell()
     n_plain, n_gen, tc, tr = runner.solver.tile_counts()
+    if world > 1:      # the timed launch covers the plain tiles that read no ghost column (hf2d_gpu_step_part S2_INNER)
+        n_plain -= runner.solver.edge_tile_counts()[0]
     plain_cells = n_plain * tc * tr
     peak, peak_src = peaks()
     b2 = stage2_bytes_per_cell(args.model)
@@ -280,7 +288,7 @@ def main():
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": f"BASELINE configs[3]: three cylinders, NS k-eps URANS (9 equations), flat, {args.nx}x{args.ny} cells per GPU "
                                    f"({args.nx * world}x{args.ny} total), X-slabs", "model": args.model,
-                       "active_cells": act, "total_cells": args.nx * args.ny * world, "seams": args.seams, "rms_every": args.rms_every,
+                       "active_cells": act, "total_cells": args.nx * args.ny * world, "seams": args.seams, "schedule": args.schedule if world > 1 else None, "rms_every": args.rms_every,
                        "tiles_per_gpu": {"plain": n_plain, "general": n_gen, "cols": tc, "rows": tr},
                        "l2": "per-step working set (~6 GB/GPU) >> 126 MB L2: no flush needed", "parallelism": f"x-slab{world}"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,

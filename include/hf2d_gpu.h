@@ -154,6 +154,26 @@ int  hf2d_gpu_step_stage1(hf2d_gpu* h);
 int  hf2d_gpu_step_stage2(hf2d_gpu* h);
 int  hf2d_gpu_step_end(hf2d_gpu* h, hf2d_step_report* report /* may be NULL: no read-back */);
 /* dt of the running minimum as device pointer (one double) so a driver can all-reduce(min) it in place */
+/* Overlapped X-slab step: the same step cut into parts that the driver queues on two stream "lanes" (0 = the handle's
+ * main stream, 1 = its high-priority side stream, hf2d_gpu_side_stream) so that seam traffic hides behind the bulk:
+ *     begin | fork | lane 1: [recv left, unpack(0,2)] PREPASS [pack(1,2), send right] S1_GENERAL | lane 0: S1_PLAIN
+ *           | join | S1_FINISH | fork
+ *           | lane 1: pack(1,1) pack(0,2) <-> unpack(0,1) unpack(1,2)  S2_EDGE  pack(.,0) <-> unpack(.,0) | lane 0: S2_INNER
+ *           | join | S2_FINISH | dt all-reduce | end
+ * (openhyperflow2d_b200/multigpu.py is that driver over torch.distributed; replaces the once-per-step blocking exchange
+ * of the reference's MPI build, deeps2d_core.cpp:1336-1400).  Between S2_EDGE and S2_FINISH halo phase 0 addresses the
+ * NEW state.  The first hf2d_gpu_edge_tile_counts() tiles of each class are the ones that read a ghost column. */
+enum hf2d_step_part_id {
+    HF2D_PART_PREPASS = 1, HF2D_PART_S1_PLAIN = 2, HF2D_PART_S1_GENERAL = 3, HF2D_PART_S1_FINISH = 4,
+    HF2D_PART_S2_INNER = 5, HF2D_PART_S2_EDGE = 6, HF2D_PART_S2_FINISH = 7
+};
+int  hf2d_gpu_step_part(hf2d_gpu* h, int part, int lane, int want_rms);
+int  hf2d_gpu_lane_fork(hf2d_gpu* h);    /* lane 1 waits for everything queued on lane 0 so far */
+int  hf2d_gpu_lane_join(hf2d_gpu* h);    /* lane 0 waits for everything queued on lane 1 so far */
+void* hf2d_gpu_side_stream(hf2d_gpu* h); /* cudaStream_t of lane 1 */
+int  hf2d_gpu_halo_pack_lane(hf2d_gpu* h, int side, int phase, void* dev_buf, int lane);
+int  hf2d_gpu_halo_unpack_lane(hf2d_gpu* h, int side, int phase, const void* dev_buf, int lane);
+int  hf2d_gpu_edge_tile_counts(hf2d_gpu* h, int* n_plain_edge, int* n_general_edge);
 int  hf2d_gpu_dt_ptr(hf2d_gpu* h, void** dev_ptr);
 void* hf2d_gpu_stream(hf2d_gpu* h);   /* cudaStream_t the handle launches on */
 int  hf2d_gpu_set_stream(hf2d_gpu* h, void* cuda_stream);   /* launch on the caller's stream instead */

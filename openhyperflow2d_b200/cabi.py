@@ -63,7 +63,9 @@ EXPORTS = ["hf2d_gpu_last_error", "hf2d_gpu_device_count", "hf2d_gpu_create", "h
            "hf2d_gpu_download_aos", "hf2d_gpu_pin_host", "hf2d_gpu_unpin_host", "hf2d_gpu_step", "hf2d_gpu_step_continue", "hf2d_gpu_read_node", "hf2d_gpu_run_cycle", "hf2d_gpu_field_ptr", "hf2d_gpu_active_cells",
            "hf2d_gpu_bytes_per_cell", "hf2d_gpu_tile_counts", "hf2d_gpu_halo_bytes", "hf2d_gpu_halo_pack", "hf2d_gpu_halo_unpack", "hf2d_gpu_step_begin",
            "hf2d_gpu_step_prepass", "hf2d_gpu_step_stage1", "hf2d_gpu_step_stage2", "hf2d_gpu_step_end", "hf2d_gpu_dt_ptr", "hf2d_gpu_stream",
-           "hf2d_gpu_set_stream", "hf2d_gpu_set_timing", "hf2d_gpu_get_timing", "hf2d_gpu_dt_export", "hf2d_gpu_dt_import", "hf2d_gpu_launch_count"]
+           "hf2d_gpu_set_stream", "hf2d_gpu_set_timing", "hf2d_gpu_get_timing", "hf2d_gpu_dt_export", "hf2d_gpu_dt_import", "hf2d_gpu_launch_count",
+           "hf2d_gpu_step_part", "hf2d_gpu_lane_fork", "hf2d_gpu_lane_join", "hf2d_gpu_side_stream", "hf2d_gpu_halo_pack_lane",
+           "hf2d_gpu_halo_unpack_lane", "hf2d_gpu_edge_tile_counts"]
 
 
 def lib():
@@ -90,6 +92,14 @@ def lib():
         L.hf2d_gpu_halo_bytes.restype = C.c_size_t
         L.hf2d_gpu_halo_pack.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.hf2d_gpu_halo_unpack.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.hf2d_gpu_halo_pack_lane.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.hf2d_gpu_halo_unpack_lane.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.hf2d_gpu_step_part.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
+        L.hf2d_gpu_lane_fork.argtypes = [C.c_void_p]
+        L.hf2d_gpu_lane_join.argtypes = [C.c_void_p]
+        L.hf2d_gpu_side_stream.argtypes = [C.c_void_p]
+        L.hf2d_gpu_side_stream.restype = C.c_void_p
+        L.hf2d_gpu_edge_tile_counts.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
         for f in ("hf2d_gpu_step_begin", "hf2d_gpu_step_prepass", "hf2d_gpu_step_stage1", "hf2d_gpu_step_stage2"):
             getattr(L, f).argtypes = [C.c_void_p]
         L.hf2d_gpu_step_end.argtypes = [C.c_void_p, C.POINTER(StepReport)]
@@ -226,11 +236,31 @@ class Solver:
     def halo_bytes(self, phase: int) -> int:
         return lib().hf2d_gpu_halo_bytes(self._h, phase)
 
-    def halo_pack(self, side: int, phase: int, dev_ptr: int):
-        _ck(lib().hf2d_gpu_halo_pack(self._h, side, phase, C.c_void_p(dev_ptr)))
+    def halo_pack(self, side: int, phase: int, dev_ptr: int, lane: int = 0):
+        _ck(lib().hf2d_gpu_halo_pack_lane(self._h, side, phase, C.c_void_p(dev_ptr), lane))
 
-    def halo_unpack(self, side: int, phase: int, dev_ptr: int):
-        _ck(lib().hf2d_gpu_halo_unpack(self._h, side, phase, C.c_void_p(dev_ptr)))
+    def halo_unpack(self, side: int, phase: int, dev_ptr: int, lane: int = 0):
+        _ck(lib().hf2d_gpu_halo_unpack_lane(self._h, side, phase, C.c_void_p(dev_ptr), lane))
+
+    # one step in parts on two stream lanes (include/hf2d_gpu.h "overlapped X-slab step")
+    PREPASS, S1_PLAIN, S1_GENERAL, S1_FINISH, S2_INNER, S2_EDGE, S2_FINISH = 1, 2, 3, 4, 5, 6, 7
+
+    def step_part(self, part: int, lane: int = 0, want_rms: int = 1):
+        _ck(lib().hf2d_gpu_step_part(self._h, part, lane, want_rms))
+
+    def lane_fork(self):
+        _ck(lib().hf2d_gpu_lane_fork(self._h))
+
+    def lane_join(self):
+        _ck(lib().hf2d_gpu_lane_join(self._h))
+
+    def side_stream(self) -> int:
+        return int(lib().hf2d_gpu_side_stream(self._h) or 0)
+
+    def edge_tile_counts(self):
+        a, b = C.c_int(), C.c_int()
+        _ck(lib().hf2d_gpu_edge_tile_counts(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
 
     def step_begin(self):
         _ck(lib().hf2d_gpu_step_begin(self._h))

@@ -30,6 +30,8 @@ struct hf2d_gpu {
     cudaStream_t stream0;           // the stream created with the handle
     cudaStream_t stream_b;          // side stream: the general (boundary) tiles run beside the plain ones
     cudaEvent_t ev_fork, ev_join;
+    cudaStream_t stream_c;          // third lane: the general tiles of hf2d_gpu_step_part(S2_INNER) beside the plain ones
+    cudaEvent_t ev_fork_c, ev_join_c;
     bool own_stream;
     cudaEvent_t ev0, ev1;
     Params P;                       // device pointers + configuration, passed by value to the kernels
@@ -56,6 +58,8 @@ struct hf2d_gpu {
     // strip-sweep tiles (hf2d_stage2.cuh): TI columns x S2_WARPS strips of STRIP_ROWS rows
     int TI, n_sb, n_tx;
     int *d_tiles_plain, *d_tiles_gen; int n_plain, n_gen;
+    int n_plain_edge, n_gen_edge;   // the first n_*_edge tiles of each list touch a ghost column (X-slab seams): hf2d_gpu_step_part
+    bool s2_pending;                // Stage-2 parts queued, planes not yet swapped (hf2d_gpu_step_part S2_FINISH does)
     int plain_ttc;                  // TurbType word of the plain tiles (-1: no plain kernel for this grid)
     // optional per-kernel timing of the two plain-tile launches (bench.py roofline): event pairs on the main stream
     bool timing; std::vector<cudaEvent_t> tev[2][2]; int tn[2];
@@ -92,7 +96,12 @@ extern "C" int hf2d_gpu_create(const hf2d_cfg* cfg, int device, hf2d_gpu** out) 
     CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     h->stream0 = h->stream; h->own_stream = true;
     CK(cudaEventCreate(&h->ev0)); CK(cudaEventCreate(&h->ev1));
-    CK(cudaStreamCreateWithFlags(&h->stream_b, cudaStreamNonBlocking));
+    {   // side stream: few, latency-bound launches (boundary tiles, seam work) that must not queue behind the bulk kernel's blocks
+        int lo = 0, hi = 0; CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        CK(cudaStreamCreateWithPriority(&h->stream_b, cudaStreamNonBlocking, hi));
+        CK(cudaStreamCreateWithPriority(&h->stream_c, cudaStreamNonBlocking, hi));
+        CK(cudaEventCreateWithFlags(&h->ev_fork_c, cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&h->ev_join_c, cudaEventDisableTiming));
+    }
     CK(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
     std::vector<DevTable> tabs(HF2D_NTABLES);
     for (int t = 0; t < HF2D_NTABLES; t++) {
@@ -124,7 +133,7 @@ extern "C" int hf2d_gpu_create(const hf2d_cfg* cfg, int device, hf2d_gpu** out) 
     P.tab = h->d_tab; P.st = h->d_st;
     h->last_iter_cycle = cfg->last_iter;
     h->rms_every = cfg->NOutStep; h->prepass_done = false; h->timing = false; h->tn[0] = h->tn[1] = 0;
-    h->TI = 16; h->n_sb = h->n_tx = 0; h->d_tiles_plain = h->d_tiles_gen = nullptr; h->n_plain = h->n_gen = 0; h->plain_ttc = -1;
+    h->TI = 16; h->n_sb = h->n_tx = 0; h->d_tiles_plain = h->d_tiles_gen = nullptr; h->n_plain = h->n_gen = 0; h->n_plain_edge = h->n_gen_edge = 0; h->s2_pending = false; h->plain_ttc = -1;
     *out = h;
     return HF2D_OK;
 }
@@ -139,7 +148,7 @@ extern "C" int hf2d_gpu_destroy(hf2d_gpu* h) {
     if (h->h_st) cudaFreeHost(h->h_st);
     cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
     for (int a = 0; a < 2; a++) for (int b = 0; b < 2; b++) for (cudaEvent_t e : h->tev[a][b]) cudaEventDestroy(e);
-    cudaStreamDestroy(h->stream0); cudaStreamDestroy(h->stream_b); cudaEventDestroy(h->ev_fork); cudaEventDestroy(h->ev_join);
+    cudaStreamDestroy(h->stream0); cudaStreamDestroy(h->stream_b); cudaStreamDestroy(h->stream_c); cudaEventDestroy(h->ev_fork_c); cudaEventDestroy(h->ev_join_c); cudaEventDestroy(h->ev_fork); cudaEventDestroy(h->ev_join);
     delete h;
     return HF2D_OK;
 }

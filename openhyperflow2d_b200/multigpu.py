@@ -32,13 +32,18 @@ class SlabProtocol:
     """The per-step exchange protocol, independent of what computes: `solver` offers the split-step / halo calls of
     cabi.Solver, buffers are torch tensors on `dev` (CUDA + NCCL in production, CPU + gloo in the protocol tests)."""
 
-    def _init_protocol(self, torch, solver, rank, world, dev, seams):
-        assert seams in ("exact", "lagged-chain")
+    def _init_protocol(self, torch, solver, rank, world, dev, seams, schedule="overlapped"):
+        assert seams in ("exact", "lagged-chain") and schedule in ("overlapped", "sequential")
         self.torch, self.solver, self.rank, self.world, self.dev, self.seams = torch, solver, rank, world, dev, seams
+        self.schedule = schedule
+        self.rms_every = getattr(self, "rms_every", None) or 1
         self.gl = 1 if (world > 1 and rank > 0) else 0
         self.gr = 1 if (world > 1 and rank < world - 1) else 0
+        self.side = None
         if world > 1:
             self._alloc(dev)
+            if dev.type == "cuda":      # lane 1 of the solver as a torch stream: collectives issued under it are ordered with it
+                self.side = torch.cuda.ExternalStream(solver.side_stream(), device=dev)
 
     def _alloc(self, dev):
         torch = self.torch
@@ -49,40 +54,65 @@ class SlabProtocol:
         self.send2, self.recv2 = [z(n2), z(n2)], [z(n2), z(n2)]
         self.dtbuf = z(1)
 
+    def _lane(self, lane):
+        """Collectives issued inside wait for, and are waited on by, that lane's stream (no-op on CPU / lane 0)."""
+        import contextlib
+        if lane == 0 or self.side is None:
+            return contextlib.nullcontext()
+        return self.torch.cuda.stream(self.side)
+
     def _batch(self, ops):
         if ops:
             for w in self.torch.distributed.batch_isend_irecv(ops):
                 w.wait()
 
-    def _mid_exchange(self):
+    def _mid_exchange(self, lane=0):
         """Between Stage 1 and Stage 2: phase 1 (left -> right) and the post-pre-pass S of the first owned column (right -> left)."""
         dist, s, ops = self.torch.distributed, self.solver, []
         if self.gr:
-            s.halo_pack(1, 1, self.send1.data_ptr()); ops.append(dist.P2POp(dist.isend, self.send1, self.rank + 1))
+            s.halo_pack(1, 1, self.send1.data_ptr(), lane); ops.append(dist.P2POp(dist.isend, self.send1, self.rank + 1))
             ops.append(dist.P2POp(dist.irecv, self.recv2[1], self.rank + 1))
         if self.gl:
-            s.halo_pack(0, 2, self.send2[0].data_ptr()); ops.append(dist.P2POp(dist.isend, self.send2[0], self.rank - 1))
+            s.halo_pack(0, 2, self.send2[0].data_ptr(), lane); ops.append(dist.P2POp(dist.isend, self.send2[0], self.rank - 1))
             ops.append(dist.P2POp(dist.irecv, self.recv1, self.rank - 1))
         self._batch(ops)
         if self.gl:
-            s.halo_unpack(0, 1, self.recv1.data_ptr())
+            s.halo_unpack(0, 1, self.recv1.data_ptr(), lane)
         if self.gr:
-            s.halo_unpack(1, 2, self.recv2[1].data_ptr())
+            s.halo_unpack(1, 2, self.recv2[1].data_ptr(), lane)
 
-    def _end_exchange(self):
-        """After Stage 2: phase 0, full edge columns both ways."""
+    def _end_exchange(self, lane=0):
+        """After Stage 2 (of the edge tiles): phase 0, full edge columns both ways."""
         dist, s, ops = self.torch.distributed, self.solver, []
         if self.gl:
-            s.halo_pack(0, 0, self.send[0].data_ptr())
+            s.halo_pack(0, 0, self.send[0].data_ptr(), lane)
             ops += [dist.P2POp(dist.isend, self.send[0], self.rank - 1), dist.P2POp(dist.irecv, self.recv[0], self.rank - 1)]
         if self.gr:
-            s.halo_pack(1, 0, self.send[1].data_ptr())
+            s.halo_pack(1, 0, self.send[1].data_ptr(), lane)
             ops += [dist.P2POp(dist.isend, self.send[1], self.rank + 1), dist.P2POp(dist.irecv, self.recv[1], self.rank + 1)]
         self._batch(ops)
         if self.gl:
-            s.halo_unpack(0, 0, self.recv[0].data_ptr())
+            s.halo_unpack(0, 0, self.recv[0].data_ptr(), lane)
         if self.gr:
-            s.halo_unpack(1, 0, self.recv[1].data_ptr())
+            s.halo_unpack(1, 0, self.recv[1].data_ptr(), lane)
+
+    def _handoff_prepass(self, lane):
+        """The ordered Neumann pre-pass; with exact seams the overwritten edge column travels left -> right in rank order."""
+        dist, s = self.torch.distributed, self.solver
+        P = type(s)
+        if self.seams == "exact" and self.gl:
+            dist.recv(self.recv2[0], self.rank - 1)
+            s.halo_unpack(0, 2, self.recv2[0].data_ptr(), lane)
+        s.step_part(P.PREPASS, lane)
+        if self.seams == "exact" and self.gr:
+            s.halo_pack(1, 2, self.send2[1].data_ptr(), lane)
+            dist.send(self.send2[1], self.rank + 1)
+
+    def _dt_allreduce(self):
+        dist, s = self.torch.distributed, self.solver
+        s.dt_export(self.dtbuf.data_ptr())
+        dist.all_reduce(self.dtbuf, op=dist.ReduceOp.MIN)
+        s.dt_import(self.dtbuf.data_ptr())
 
     # ---- stepping ----
     def step(self, n):
@@ -91,29 +121,51 @@ class SlabProtocol:
             rep = s.step(n)
             self.launches_last = rep.kernel_launches
             return rep
-        dist = self.torch.distributed
-        for _ in range(n):
-            s.step_begin()
-            if self.seams == "exact":     # rank-ordered hand-off of the overwritten edge column (phase 2, left -> right)
-                if self.gl:
-                    dist.recv(self.recv2[0], self.rank - 1)
-                    s.halo_unpack(0, 2, self.recv2[0].data_ptr())
-                s.step_prepass()
-                if self.gr:
-                    s.halo_pack(1, 2, self.send2[1].data_ptr())
-                    dist.send(self.send2[1], self.rank + 1)
-            s.step_stage1()
-            self._mid_exchange()
-            s.step_stage2()
-            self._end_exchange()
-            s.dt_export(self.dtbuf.data_ptr())
-            dist.all_reduce(self.dtbuf, op=dist.ReduceOp.MIN)
-            s.dt_import(self.dtbuf.data_ptr())
-            s.step_end()
+        for q in range(n):
+            want_rms = 1 if (q == n - 1 or self.rms_every <= 1 or q % self.rms_every == 0) else 0
+            (self._step_overlapped if self.schedule == "overlapped" else self._step_sequential)(want_rms)
         return None
 
+    def _step_sequential(self, want_rms):
+        """Everything on one stream, exchanges between the stages (the straightforward schedule; kept as the baseline)."""
+        s = self.solver
+        P = type(s)
+        s.step_begin()
+        self._handoff_prepass(0)
+        s.step_part(P.S1_GENERAL, 0); s.step_part(P.S1_PLAIN, 0); s.step_part(P.S1_FINISH, 0)
+        self._mid_exchange()
+        s.step_part(P.S2_EDGE, 0, want_rms); s.step_part(P.S2_INNER, 0, want_rms)
+        self._end_exchange()
+        s.step_part(P.S2_FINISH, 0)
+        self._dt_allreduce()
+        s.step_end()
+
+    def _step_overlapped(self, want_rms):
+        """Seam work on lane 1 (high-priority side stream), bulk tiles on lane 0: see include/hf2d_gpu.h."""
+        s = self.solver
+        P = type(s)
+        s.step_begin()
+        s.lane_fork()
+        with self._lane(1):
+            self._handoff_prepass(1)
+            s.step_part(P.S1_GENERAL, 1)
+        s.step_part(P.S1_PLAIN, 0)
+        s.lane_join()
+        s.step_part(P.S1_FINISH, 0)
+        s.lane_fork()
+        with self._lane(1):
+            self._mid_exchange(1)
+            s.step_part(P.S2_EDGE, 1, want_rms)
+            self._end_exchange(1)
+        s.step_part(P.S2_INNER, 0, want_rms)
+        s.lane_join()
+        s.step_part(P.S2_FINISH, 0)
+        self._dt_allreduce()
+        s.step_end()
+
+
 class SlabRunner(SlabProtocol):
-    def __init__(self, nx, ny, model="keps", rank=0, world=1, device=0, seams="exact", rms_every=None):
+    def __init__(self, nx, ny, model="keps", rank=0, world=1, device=0, seams="exact", rms_every=None, schedule="overlapped"):
         import torch
         self.device = device
         gl = 1 if (world > 1 and rank > 0) else 0
@@ -124,7 +176,8 @@ class SlabRunner(SlabProtocol):
         solver.set_stream(torch.cuda.current_stream().cuda_stream)
         solver.upload_aos(J)
         self.launches_last = 0
-        self._init_protocol(torch, solver, rank, world, torch.device("cuda", device), seams)
+        self.rms_every = rms_every
+        self._init_protocol(torch, solver, rank, world, torch.device("cuda", device), seams, schedule)
 
     # ---- collectives ----
     def barrier(self):

@@ -230,6 +230,132 @@ def _slab_run(model, nx, ny, nsteps, world):
     return out, Jfull, cfg, lay
 
 
+def _slab_run_parts(model, nx, ny, nsteps, world):
+    """The same slabs driven through the OVERLAPPED schedule's calls (hf2d_gpu_step_part on two stream lanes, halo phase 0
+    packed while Stage 2 is pending): what SlabProtocol._step_overlapped issues per rank, minus the transport."""
+    import torch
+    from openhyperflow2d_b200 import cabi, gridgen
+    w = nx // world
+    Jfull, cfg, lay = gridgen.three_cylinders(nx, ny, model=model)
+    slabs = []
+    for r in range(world):
+        gl, gr = (1 if r > 0 else 0), (1 if r < world - 1 else 0)
+        J = np.array(Jfull[r * w - gl:(r + 1) * w + gr], copy=True)
+        c = dict(cfg); c["MaxX"] = J.shape[0]
+        s = cabi.Solver(c, lay, rank=r, n_ranks=world)
+        s.upload_aos(J)
+        slabs.append((s, J, gl, gr))
+    dev = torch.device("cuda", 0)
+    S = cabi.Solver
+    z = lambda ph: torch.zeros(slabs[0][0].halo_bytes(ph) // 8, dtype=torch.float64, device=dev)
+    buf0 = [[z(0), z(0)] for _ in range(world)]
+    buf1 = [z(1) for _ in range(world)]
+    buf2 = [z(2) for _ in range(world)]
+    dtb = torch.zeros(world, dtype=torch.float64, device=dev)
+    sync = torch.cuda.synchronize
+    for q in range(nsteps):
+        for r, (s, J, gl, gr) in enumerate(slabs):      # lane 1: hand-off + pre-pass in rank order, then the general tiles
+            s.step_begin(); s.lane_fork()
+            if gl:
+                s.halo_unpack(0, 2, buf2[r - 1].data_ptr(), 1)
+            s.step_part(S.PREPASS, 1)
+            if gr:
+                s.halo_pack(1, 2, buf2[r].data_ptr(), 1)
+            s.step_part(S.S1_GENERAL, 1)
+            s.step_part(S.S1_PLAIN, 0)                  # lane 0 beside it
+            sync()
+        for s, *_ in slabs:
+            s.lane_join(); s.step_part(S.S1_FINISH, 0); s.lane_fork()
+        for r, (s, J, gl, gr) in enumerate(slabs):
+            s.step_part(S.S2_INNER, 0, 1)               # the bulk starts before the seam data has moved
+            if gr:
+                s.halo_pack(1, 1, buf1[r].data_ptr(), 1)
+            if gl:
+                s.halo_pack(0, 2, buf2[r].data_ptr(), 1)
+        sync()
+        for r, (s, J, gl, gr) in enumerate(slabs):
+            if gl:
+                s.halo_unpack(0, 1, buf1[r - 1].data_ptr(), 1)
+            if gr:
+                s.halo_unpack(1, 2, buf2[r + 1].data_ptr(), 1)
+            s.step_part(S.S2_EDGE, 1, 1)
+            if gl:                                      # phase 0 while Stage 2 is pending: addresses the NEW state
+                s.halo_pack(0, 0, buf0[r][0].data_ptr(), 1)
+            if gr:
+                s.halo_pack(1, 0, buf0[r][1].data_ptr(), 1)
+        sync()
+        for r, (s, J, gl, gr) in enumerate(slabs):
+            if gl:
+                s.halo_unpack(0, 0, buf0[r - 1][1].data_ptr(), 1)
+            if gr:
+                s.halo_unpack(1, 0, buf0[r + 1][0].data_ptr(), 1)
+            s.lane_join(); s.step_part(S.S2_FINISH, 0)
+            s.dt_export(dtb[r:r + 1].data_ptr())
+        sync()
+        dtb[:] = dtb.min()
+        for r, (s, *_rest) in enumerate(slabs):
+            s.dt_import(dtb[r:r + 1].data_ptr())
+            s.step_end()
+        sync()
+    out = np.array(Jfull, copy=True)
+    for r, (s, J, gl, gr) in enumerate(slabs):
+        s.download_aos(J)
+        out[r * w:(r + 1) * w] = J[gl:J.shape[0] - gr]
+        s.close()
+    return out
+
+
+@pytest.mark.parametrize("model", ["laminar", "keps"])
+def test_overlapped_schedule_reproduces_single_domain(model):
+    nx, ny, nsteps = 96, 160, 5
+    ref, *_ = _slab_run(model, nx, ny, nsteps, 1)
+    for world in (2, 3):
+        got = _slab_run_parts(model, nx, ny, nsteps, world)
+        for f in GPU_FIELDS + NS_FIELDS:
+            a, b = np.asarray(got[f], float), np.asarray(ref[f], float)
+            same = (a == b) | ((a != a) & (b != b))
+            assert same.all(), f"{model} x{world}: {f} differs in {int((~same).sum())} entries, rel-Linf {rel_linf(a, b):.3e}"
+
+
+def _nccl_worker(rank, world, port, model, nx, ny, nsteps, schedule, out_dir):
+    import torch
+    import torch.distributed as dist
+    from openhyperflow2d_b200.multigpu import SlabRunner
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    r = SlabRunner(nx // world, ny, model=model, rank=rank, world=world, device=rank, schedule=schedule, rms_every=3)
+    r.step(nsteps)
+    J = np.array(r.J, copy=True)
+    r.solver.download_aos(J)
+    np.save(f"{out_dir}/r{rank}.npy", J[r.gl:J.shape[0] - r.gr].view(np.uint8))
+    r.barrier()
+    r.close()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("schedule", ["overlapped", "sequential"])
+def test_nccl_slabs_reproduce_single_domain(schedule, tmp_path):
+    """SlabRunner over NCCL on every GPU of the box (needs >= 2): bit-identical with the single-domain run."""
+    import socket
+    import torch
+    import torch.multiprocessing as mp
+    world = min(torch.cuda.device_count(), 4)
+    if world < 2:
+        pytest.skip("needs at least 2 GPUs")
+    model, nx, ny, nsteps = "keps", 192, 160, 7
+    ref, *_ = _slab_run(model, nx, ny, nsteps, 1)
+    with socket.socket() as sk:
+        sk.bind(("127.0.0.1", 0)); port = sk.getsockname()[1]
+    mp.spawn(_nccl_worker, args=(world, port, model, nx, ny, nsteps, schedule, str(tmp_path)), nprocs=world, join=True)
+    w = nx // world
+    for r in range(world):
+        got = np.load(tmp_path / f"r{r}.npy").view(ref.dtype).reshape(w, ny)
+        for f in GPU_FIELDS + NS_FIELDS:
+            a, b = np.asarray(got[f], float), np.asarray(ref[r * w:(r + 1) * w][f], float)
+            same = (a == b) | ((a != a) & (b != b))
+            assert same.all(), f"rank {r}: {f} differs in {int((~same).sum())} entries, rel-Linf {rel_linf(a, b):.3e}"
+
+
 @pytest.mark.parametrize("model", ["laminar", "keps"])
 def test_x_slabs_reproduce_single_domain(model):
     """Two and four X-slabs with the exact-seam exchange (halo phases 2, 1, 0) give the single-domain result BIT FOR BIT,

@@ -28,6 +28,7 @@ class FakeSolver:
         self.S = np.array(full[g0 - self.gl:g0 + w + self.gr], copy=True)
         self.SN = np.zeros_like(self.S)
         self.S0 = np.zeros_like(self.S)
+        self.new = None          # Stage-2 output while its parts are pending (phase 0 then addresses the NEW state)
         self.nx = self.S.shape[0]
         self.lo, self.hi = self.gl, self.nx - self.gr
         self.dt = 1.0
@@ -53,14 +54,46 @@ class FakeSolver:
             r = self.S0[i + 1] if i + 1 < self.nx else self.S[i]
             self.SN[i] = self.S[i] * 0.75 + 0.125 * (l + r) + 0.01
 
-    def step_stage2(self):
-        new = np.array(self.S, copy=True)
-        for i in range(self.lo, self.hi):
+    def _s2_columns(self, cols):
+        if self.new is None:
+            self.new = np.array(self.S, copy=True)
+        for i in cols:
             l_new = self.SN[i - 1] * 1.5 if i > 0 else self.SN[i] * 1.5     # left neighbour: recomputed NEW state (needs its SN)
             r_old = self.S[i + 1] if i + 1 < self.nx else self.S[i]           # right neighbour: after this step's pre-pass
-            new[i] = self.SN[i] + 0.0625 * (r_old - l_new / 1.5)
-        self.S = new
-        self.dt = min(self.dt, float(1.0 / (1.0 + np.abs(new[self.lo:self.hi]).max())))
+            self.new[i] = self.SN[i] + 0.0625 * (r_old - l_new / 1.5)
+
+    def _edge_columns(self):
+        return ([self.lo] if self.gl else []) + ([self.hi - 1] if self.gr else [])
+
+    def step_stage2(self):
+        self._s2_columns(range(self.lo, self.hi))
+        self._s2_finish()
+
+    def _s2_finish(self):
+        self.S, self.new = self.new, None
+        self.dt = min(self.dt, float(1.0 / (1.0 + np.abs(self.S[self.lo:self.hi]).max())))
+
+    # --- the step in parts (cabi.Solver.step_part); lanes are streams on the GPU, nothing here ---
+    PREPASS, S1_PLAIN, S1_GENERAL, S1_FINISH, S2_INNER, S2_EDGE, S2_FINISH = 1, 2, 3, 4, 5, 6, 7
+
+    def step_part(self, part, lane=0, want_rms=1):
+        if part == self.PREPASS:
+            self.step_prepass()
+        elif part == self.S1_GENERAL:
+            self.step_stage1()
+        elif part == self.S2_INNER:
+            e = self._edge_columns()
+            self._s2_columns([i for i in range(self.lo, self.hi) if i not in e])
+        elif part == self.S2_EDGE:
+            self._s2_columns(self._edge_columns())
+        elif part == self.S2_FINISH:
+            self._s2_finish()
+
+    def lane_fork(self):
+        pass
+
+    def lane_join(self):
+        pass
 
     def step_end(self, want_report=False):
         pass
@@ -69,21 +102,21 @@ class FakeSolver:
     def halo_bytes(self, phase):
         return (2 if phase == 0 else 1) * NY * 8
 
-    def halo_pack(self, side, phase, ptr):
+    def halo_pack(self, side, phase, ptr, lane=0):
         col = 1 if side == 0 else self.nx - 2
         b = _view(ptr, self.halo_bytes(phase) // 8)
         if phase == 0:
-            b[:NY], b[NY:] = self.S[col], self.SN[col]
+            b[:NY], b[NY:] = (self.S if self.new is None else self.new)[col], self.SN[col]
         elif phase == 1:
             b[:] = self.SN[col]
         else:
             b[:] = self.S[col]
 
-    def halo_unpack(self, side, phase, ptr):
+    def halo_unpack(self, side, phase, ptr, lane=0):
         col = 0 if side == 0 else self.nx - 1
         b = _view(ptr, self.halo_bytes(phase) // 8)
         if phase == 0:
-            self.S[col], self.SN[col] = b[:NY], b[NY:]
+            (self.S if self.new is None else self.new)[col], self.SN[col] = b[:NY], b[NY:]
         elif phase == 1:
             self.SN[col] = b
         else:
@@ -101,7 +134,7 @@ def _field(nx):
     return rng.uniform(0.5, 2.0, size=(nx, NY))
 
 
-def _worker(rank, world, port, nx, nsteps, seams, out_dir):
+def _worker(rank, world, port, nx, nsteps, seams, out_dir, schedule="overlapped"):
     import torch
     import torch.distributed as dist
     from openhyperflow2d_b200.multigpu import SlabProtocol
@@ -109,7 +142,7 @@ def _worker(rank, world, port, nx, nsteps, seams, out_dir):
     w = nx // world
     fs = FakeSolver(_field(nx), rank * w, w, rank, world)
     p = SlabProtocol()
-    p._init_protocol(torch, fs, rank, world, torch.device("cpu"), seams)
+    p._init_protocol(torch, fs, rank, world, torch.device("cpu"), seams, schedule)
     p.step(nsteps)
     np.save(os.path.join(out_dir, f"r{rank}.npy"), np.concatenate([fs.S[fs.lo:fs.hi].ravel(), [fs.dt]]))
     dist.barrier()
@@ -122,14 +155,14 @@ def _free_port():
         return s.getsockname()[1]
 
 
-@pytest.mark.parametrize("world", [2, 3])
-def test_exact_seams_reproduce_single_domain(world, tmp_path):
+@pytest.mark.parametrize("world,schedule", [(2, "overlapped"), (3, "overlapped"), (2, "sequential")])
+def test_exact_seams_reproduce_single_domain(world, schedule, tmp_path):
     import torch.multiprocessing as mp
     nx, nsteps = 12, 4
     ref = FakeSolver(_field(nx), 0, nx, 0, 1)
     for _ in range(nsteps):
         ref.step_begin(); ref.step_stage1(); ref.step_stage2(); ref.step_end()
-    mp.spawn(_worker, args=(world, _free_port(), nx, nsteps, "exact", str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), nx, nsteps, "exact", str(tmp_path), schedule), nprocs=world, join=True)
     got = [np.load(tmp_path / f"r{r}.npy") for r in range(world)]
     S = np.concatenate([g[:-1] for g in got]).reshape(nx, NY)
     assert (S == ref.S).all()
