@@ -156,7 +156,7 @@ int  hf2d_gpu_step_end(hf2d_gpu* h, hf2d_step_report* report /* may be NULL: no 
 /* dt of the running minimum as device pointer (one double) so a driver can all-reduce(min) it in place */
 /* Overlapped X-slab step: the same step cut into parts that the driver queues on two stream "lanes" (0 = the handle's
  * main stream, 1 = its high-priority side stream, hf2d_gpu_side_stream) so that seam traffic hides behind the bulk:
- *     begin | fork | lane 1: [recv left, unpack(0,2)] PREPASS [pack(1,2), send right] S1_GENERAL | lane 0: S1_PLAIN
+ *     begin | fork | lane 1: PREPASS_LOCAL [recv left, unpack(0,2)] PREPASS [pack(1,2), send right] S1_GENERAL | lane 0: S1_PLAIN
  *           | join | S1_FINISH | fork
  *           | lane 1: pack(1,1) pack(0,2) <-> unpack(0,1) unpack(1,2)  S2_EDGE  pack(.,0) <-> unpack(.,0) | lane 0: S2_INNER
  *           | join | S2_FINISH | dt all-reduce | end
@@ -165,7 +165,9 @@ int  hf2d_gpu_step_end(hf2d_gpu* h, hf2d_step_report* report /* may be NULL: no 
  * NEW state.  The first hf2d_gpu_edge_tile_counts() tiles of each class are the ones that read a ghost column. */
 enum hf2d_step_part_id {
     HF2D_PART_PREPASS = 1, HF2D_PART_S1_PLAIN = 2, HF2D_PART_S1_GENERAL = 3, HF2D_PART_S1_FINISH = 4,
-    HF2D_PART_S2_INNER = 5, HF2D_PART_S2_EDGE = 6, HF2D_PART_S2_FINISH = 7
+    HF2D_PART_S2_INNER = 5, HF2D_PART_S2_EDGE = 6, HF2D_PART_S2_FINISH = 7,
+    HF2D_PART_PREPASS_LOCAL = 8   /* optional, before the phase-2 receive: the part of the pre-pass that does not wait for it;
+                                     PREPASS then runs only what depends on the received column */
 };
 int  hf2d_gpu_step_part(hf2d_gpu* h, int part, int lane, int want_rms);
 int  hf2d_gpu_lane_fork(hf2d_gpu* h);    /* lane 1 waits for everything queued on lane 0 so far */

@@ -64,7 +64,7 @@ __global__ void k_neumann_level(Params P, const int* __restrict__ list, int firs
         const unsigned f = eq_flags(ct, tt, k, P.ns);
         if (!(f & 1)) continue;
         double* Sk = P.S_in + (long long)k * N;
-        double sc = Sk[n];
+        double sc = sp.S0[k];      // the node's own pre-overwrite value (k_neumann_save): re-evaluation after a hand-off is idempotent
         bool wr = false;
         if (!(f & 2)) {   // :998  (weights are crossed in x: left*n2 + right*n1)
             const double sl = n1 ? Sk[nL] : sc;
@@ -85,41 +85,82 @@ __global__ void k_neumann_level(Params P, const int* __restrict__ list, int firs
 // Chains: when an overwritten S[k] of a node depends on the overwritten S[k] of its left/down neighbour (e.g. the
 // eps equation along a whole d/dy=0 row, a side effect of the flag quirk at deeps2d_core.cpp:918-930) the values
 // form a first-order recurrence that must be evaluated in sweep order to stay bit-exact.  k_neumann_level has
-// already produced every link-free value; one warp per chain then walks its links, carrying the running value
-// in a register; the `other` operands do not depend on the carry, so their loads overlap.
-// One WARP per chain: the links are fetched 32 at a time (each lane loads one link record and its `other` operand, so
-// the two dependent global loads are paid once per 32 links instead of once per link), then the recurrence is replayed
-// in order with warp broadcasts; every lane carries the running value, lane t keeps the result of link t.
-__global__ void __launch_bounds__(32) k_neumann_chains(Params P, const int* __restrict__ chain_start, const int* __restrict__ chain_src,
-                                                       const ChainElem* __restrict__ el, int n_chains) {
-    const int c = blockIdx.x, lane = threadIdx.x;
+// already produced every link-free value; the chain kernel then walks the links, carrying the running value in a
+// register.  (A first version fetched 32 links per warp iteration: two dependent global-load latencies per 32 links,
+// 117 us for a 2048-link row; staging whole chunks first removes them from the walk.)
+#define CHAIN_THREADS 256
+#define CHAIN_CHUNK   1024      // links staged per pass: 4 per thread
+__global__ void __launch_bounds__(CHAIN_THREADS) k_neumann_chains(Params P, const int* __restrict__ chain_start, const int* __restrict__ chain_src,
+                                                                  const ChainElem* __restrict__ el, int n_chains) {
+    // One BLOCK per chain.  All threads stage CHAIN_CHUNK links at once (link record, then its `other` operand: the two
+    // dependent global loads are in flight for the whole chunk together), warp 0 replays the recurrence from shared
+    // memory 32 links at a time (broadcasts issue ahead of the carry: critical path mul -> add -> mul per link), then all
+    // threads write the results.  None of the operands is produced by a chain (hf2d_io.inc), so staging ahead is safe.
+    __shared__ double s_t[CHAIN_CHUNK];
+    __shared__ float2 s_w[CHAIN_CHUNK];
+    const int c = blockIdx.x, tid = threadIdx.x, lane = tid & 31;
     if (c >= n_chains) return;
     const int e0 = chain_start[c], e1 = chain_start[c + 1];
     const long long N = P.N;
-    double carry = P.S_in[(long long)el[e0].k * N + chain_src[c]];
-    // software pipeline: operands of the next 32 links are loaded while the current 32 are replayed
-    ChainElem q; double t = 0.; q.node = 0; q.k = 0; q.wc = q.wo = q.sc = 0.f; q.other = 0; q.other_spec = 0;
-    auto fetch = [&](int e, ChainElem& qq, double& tt) {
-        if (e < e1) {
-            qq = el[e];
-            const double o = qq.other_spec ? P.spec[qq.other].S0[qq.k] : P.S_in[(long long)qq.k * N + qq.other];
-            tt = o * (double)qq.wo;
+    double carry = 0.;
+    if (tid < 32) carry = P.S_in[(long long)el[e0].k * N + chain_src[c]];
+    for (int eb = e0; eb < e1; eb += CHAIN_CHUNK) {
+        const int cnt = min(CHAIN_CHUNK, e1 - eb);
+        int node[CHAIN_CHUNK / CHAIN_THREADS]; short kk[CHAIN_CHUNK / CHAIN_THREADS];
+#pragma unroll
+        for (int m = 0; m < CHAIN_CHUNK / CHAIN_THREADS; m++) {
+            const int i = tid + m * CHAIN_THREADS;
+            node[m] = -1; kk[m] = 0;
+            if (i < cnt) {
+                const ChainElem q = el[eb + i];
+                const double o = q.other_spec ? P.spec[q.other].S0[q.k] : P.S_in[(long long)q.k * N + q.other];
+                s_t[i] = o * (double)q.wo;
+                s_w[i] = make_float2(q.wc, q.sc);
+                node[m] = q.node; kk[m] = q.k;
+            }
         }
-    };
-    fetch(e0 + lane, q, t);
-    for (int eb = e0; eb < e1; eb += 32) {
-        ChainElem qn = q; double tn = 0.;
-        fetch(eb + 32 + lane, qn, tn);
-        const int cnt = min(32, e1 - eb);
-        double mine = 0.;
-        for (int s = 0; s < cnt; s++) {
-            const double ts = __shfl_sync(0xffffffffu, t, s);
-            const float wc = __shfl_sync(0xffffffffu, q.wc, s), sc = __shfl_sync(0xffffffffu, q.sc, s);
-            carry = (carry * (double)wc + ts) * (double)sc;
-            if (s == lane) mine = carry;
+        __syncthreads();
+        if (tid < 32) {
+            for (int b0 = 0; b0 < cnt; b0 += 32) {
+                const int n32 = min(32, cnt - b0);
+                double t = 0., wcd = 0., scd = 0.;
+                if (lane < n32) { t = s_t[b0 + lane]; const float2 w = s_w[b0 + lane]; wcd = (double)w.x; scd = (double)w.y; }
+                double mine = 0.;
+                // weight 1 on the carried value (the usual case: both x- or y-neighbours present): x * 1.0 == x exactly,
+                // so that multiplication leaves the dependent chain
+                const bool w1 = __all_sync(0xffffffffu, wcd == 1.0);
+                if (n32 == 32 && w1) {
+#pragma unroll
+                    for (int q = 0; q < 32; q++) {
+                        const double ts = __shfl_sync(0xffffffffu, t, q);
+                        const double sc = __shfl_sync(0xffffffffu, scd, q);
+                        carry = (carry + ts) * sc;
+                        if (q == lane) mine = carry;
+                    }
+                } else if (n32 == 32) {
+#pragma unroll
+                    for (int q = 0; q < 32; q++) {
+                        const double ts = __shfl_sync(0xffffffffu, t, q);
+                        const double wc = __shfl_sync(0xffffffffu, wcd, q), sc = __shfl_sync(0xffffffffu, scd, q);
+                        carry = (carry * wc + ts) * sc;
+                        if (q == lane) mine = carry;
+                    }
+                } else {
+                    for (int q = 0; q < n32; q++) {
+                        const double ts = __shfl_sync(0xffffffffu, t, q);
+                        const double wc = __shfl_sync(0xffffffffu, wcd, q), sc = __shfl_sync(0xffffffffu, scd, q);
+                        carry = (carry * wc + ts) * sc;
+                        if (q == lane) mine = carry;
+                    }
+                }
+                if (lane < n32) s_t[b0 + lane] = mine;
+            }
         }
-        if (lane < cnt) P.S_in[(long long)q.k * N + q.node] = mine;
-        q = qn; t = tn;
+        __syncthreads();
+#pragma unroll
+        for (int m = 0; m < CHAIN_CHUNK / CHAIN_THREADS; m++)
+            if (node[m] >= 0) P.S_in[(long long)kk[m] * N + node[m]] = s_t[tid + m * CHAIN_THREADS];
+        __syncthreads();
     }
 }
 

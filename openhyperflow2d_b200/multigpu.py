@@ -101,6 +101,7 @@ class SlabProtocol:
         dist, s = self.torch.distributed, self.solver
         P = type(s)
         if self.seams == "exact" and self.gl:
+            s.step_part(P.PREPASS_LOCAL, lane)      # all that does not depend on the left neighbour's column goes ahead of the wait
             dist.recv(self.recv2[0], self.rank - 1)
             s.halo_unpack(0, 2, self.recv2[0].data_ptr(), lane)
         s.step_part(P.PREPASS, lane)

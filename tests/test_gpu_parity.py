@@ -257,6 +257,7 @@ def _slab_run_parts(model, nx, ny, nsteps, world):
         for r, (s, J, gl, gr) in enumerate(slabs):      # lane 1: hand-off + pre-pass in rank order, then the general tiles
             s.step_begin(); s.lane_fork()
             if gl:
+                s.step_part(S.PREPASS_LOCAL, 1)          # what does not wait for the left neighbour's column
                 s.halo_unpack(0, 2, buf2[r - 1].data_ptr(), 1)
             s.step_part(S.PREPASS, 1)
             if gr:

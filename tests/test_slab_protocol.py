@@ -74,7 +74,7 @@ class FakeSolver:
         self.dt = min(self.dt, float(1.0 / (1.0 + np.abs(self.S[self.lo:self.hi]).max())))
 
     # --- the step in parts (cabi.Solver.step_part); lanes are streams on the GPU, nothing here ---
-    PREPASS, S1_PLAIN, S1_GENERAL, S1_FINISH, S2_INNER, S2_EDGE, S2_FINISH = 1, 2, 3, 4, 5, 6, 7
+    PREPASS, S1_PLAIN, S1_GENERAL, S1_FINISH, S2_INNER, S2_EDGE, S2_FINISH, PREPASS_LOCAL = 1, 2, 3, 4, 5, 6, 7, 8
 
     def step_part(self, part, lane=0, want_rms=1):
         if part == self.PREPASS:
