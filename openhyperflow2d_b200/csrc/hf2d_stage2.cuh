@@ -51,7 +51,9 @@ __device__ __forceinline__ void cp_async8(double* smem_dst, const double* gsrc) 
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 #define S2_TILE_DOUBLES (PL_COUNT * TILE_ROWS)          // one staged column of one warp
+#ifndef S2_WARPS
 #define S2_WARPS 4               // warps (strips) per block
+#endif
 #ifndef S2_STAGE
 #define S2_STAGE 1               // 1: plain tiles stage their columns in shared memory with cp.async
 #endif
@@ -63,12 +65,16 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // S2_WARPS consecutive entries of the tile list per block
 template <class KC>
 #ifndef S2_MINB_PLAIN
-#define S2_MINB_PLAIN 3
+#define S2_MINB_PLAIN 2     // 255 registers, 8 warps/SM: beats 3 blocks (168 registers, 288 B/thread of spills that miss L1) by 4% (profiles/NOTES.md)
 #endif
 #ifndef S2_MINB_GEN
 #define S2_MINB_GEN 3
 #endif
+#ifdef S2_MAXNREG      /* tuning builds: explicit register cap instead of a resident-block target */
+__global__ void __maxnreg__(S2_MAXNREG)
+#else
 __global__ void __launch_bounds__(S2_THREADS, KC::plain ? S2_MINB_PLAIN : S2_MINB_GEN)
+#endif
 k_stage2(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI, int want_rms) {
     __shared__ double sh_acc[S2_WARPS][2 * NEQ];               // RMS, sumDiv partial sums of the warp (want_rms steps)
     __shared__ unsigned long long sh_u[S2_WARPS][2 * NEQ + 2]; // counts, max DD, dt-min, first error
