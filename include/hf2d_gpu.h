@@ -166,6 +166,9 @@ int  hf2d_gpu_step_end(hf2d_gpu* h, hf2d_step_report* report /* may be NULL: no 
 enum hf2d_step_part_id {
     HF2D_PART_PREPASS = 1, HF2D_PART_S1_PLAIN = 2, HF2D_PART_S1_GENERAL = 3, HF2D_PART_S1_FINISH = 4,
     HF2D_PART_S2_INNER = 5, HF2D_PART_S2_EDGE = 6, HF2D_PART_S2_FINISH = 7,
+    HF2D_PART_AHEAD = 9,          /* on lane 1 after the phase-0 exchange, exact seams: the NEXT step's pre-pass + hand-off run now, hidden
+                                     behind S2_INNER (they touch only nodes of general tiles, all of which have finished Stage 2);
+                                     the next step then starts at S1_GENERAL.  Not before a download: S would hold the overwrite. */
     HF2D_PART_PREPASS_LOCAL = 8   /* optional, before the phase-2 receive: the part of the pre-pass that does not wait for it;
                                      PREPASS then runs only what depends on the received column */
 };

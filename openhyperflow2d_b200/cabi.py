@@ -243,7 +243,7 @@ class Solver:
         _ck(lib().hf2d_gpu_halo_unpack_lane(self._h, side, phase, C.c_void_p(dev_ptr), lane))
 
     # one step in parts on two stream lanes (include/hf2d_gpu.h "overlapped X-slab step")
-    PREPASS, S1_PLAIN, S1_GENERAL, S1_FINISH, S2_INNER, S2_EDGE, S2_FINISH, PREPASS_LOCAL = 1, 2, 3, 4, 5, 6, 7, 8
+    PREPASS, S1_PLAIN, S1_GENERAL, S1_FINISH, S2_INNER, S2_EDGE, S2_FINISH, PREPASS_LOCAL, AHEAD = 1, 2, 3, 4, 5, 6, 7, 8, 9
 
     def step_part(self, part: int, lane: int = 0, want_rms: int = 1):
         _ck(lib().hf2d_gpu_step_part(self._h, part, lane, want_rms))

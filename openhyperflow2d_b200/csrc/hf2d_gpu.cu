@@ -52,6 +52,7 @@ struct hf2d_gpu {
     int n_chains_local;             // chains [0, n_chains_local) do not touch the first owned column: no hand-off needed
     int* d_nlist_seam; int n_nlist_seam;   // Neumann-list nodes of the first owned column of a slab with a left neighbour
     bool prepass_local_done;
+    bool ahead;                     // between hf2d_gpu_step_part AHEAD and S2_FINISH: pre-pass / halo phase 2 address the next step's planes
     long long n_active;
     unsigned last_iter_cycle;       // last_iter of the reference (fixed during one cycle)
     uint64_t launches;
@@ -136,7 +137,7 @@ extern "C" int hf2d_gpu_create(const hf2d_cfg* cfg, int device, hf2d_gpu** out) 
     P.tab = h->d_tab; P.st = h->d_st;
     h->last_iter_cycle = cfg->last_iter;
     h->rms_every = cfg->NOutStep; h->prepass_done = false; h->timing = false; h->tn[0] = h->tn[1] = 0;
-    h->TI = 16; h->n_sb = h->n_tx = 0; h->d_tiles_plain = h->d_tiles_gen = nullptr; h->n_plain = h->n_gen = 0; h->n_plain_edge = h->n_gen_edge = 0; h->s2_pending = false; h->n_chains_local = 0; h->d_nlist_seam = nullptr; h->n_nlist_seam = 0; h->prepass_local_done = false; h->plain_ttc = -1;
+    h->TI = 16; h->n_sb = h->n_tx = 0; h->d_tiles_plain = h->d_tiles_gen = nullptr; h->n_plain = h->n_gen = 0; h->n_plain_edge = h->n_gen_edge = 0; h->s2_pending = false; h->n_chains_local = 0; h->d_nlist_seam = nullptr; h->n_nlist_seam = 0; h->prepass_local_done = false; h->ahead = false; h->plain_ttc = -1;
     *out = h;
     return HF2D_OK;
 }

@@ -124,7 +124,12 @@ class SlabProtocol:
             return rep
         for q in range(n):
             want_rms = 1 if (q == n - 1 or self.rms_every <= 1 or q % self.rms_every == 0) else 0
-            (self._step_overlapped if self.schedule == "overlapped" else self._step_sequential)(want_rms)
+            if self.schedule == "overlapped":
+                # the next step's pre-pass + hand-off run inside this step's Stage 2 -- except before the caller gets
+                # the grid back (S would hold the next step's Neumann overwrite)
+                self._step_overlapped(want_rms, ahead=(self.seams == "exact" and q < n - 1))
+            else:
+                self._step_sequential(want_rms)
         return None
 
     def _step_sequential(self, want_rms):
@@ -141,24 +146,32 @@ class SlabProtocol:
         self._dt_allreduce()
         s.step_end()
 
-    def _step_overlapped(self, want_rms):
+    def _step_overlapped(self, want_rms, ahead=False):
         """Seam work on lane 1 (high-priority side stream), bulk tiles on lane 0: see include/hf2d_gpu.h."""
         s = self.solver
         P = type(s)
         s.step_begin()
         s.lane_fork()
         with self._lane(1):
-            self._handoff_prepass(1)
+            if not getattr(self, "_prepass_ahead", False):
+                self._handoff_prepass(1)
             s.step_part(P.S1_GENERAL, 1)
         s.step_part(P.S1_PLAIN, 0)
         s.lane_join()
         s.step_part(P.S1_FINISH, 0)
         s.lane_fork()
+        s.step_part(P.S2_INNER, 0, want_rms)     # the bulk is queued first: nothing below waits for it
         with self._lane(1):
             self._mid_exchange(1)
             s.step_part(P.S2_EDGE, 1, want_rms)
             self._end_exchange(1)
-        s.step_part(P.S2_INNER, 0, want_rms)
+            if ahead:
+                # Every node the Neumann pre-pass reads or writes lies in a general tile, and those have all finished
+                # Stage 2 by now (AHEAD waits for them): the rank-ordered hand-off chain of the NEXT step -- 7 serial
+                # hops on 8 GPUs -- runs here, behind S2_INNER, instead of in front of the next Stage 1.
+                s.step_part(P.AHEAD, 1)
+                self._handoff_prepass(1)
+        self._prepass_ahead = bool(ahead)
         s.lane_join()
         s.step_part(P.S2_FINISH, 0)
         self._dt_allreduce()

@@ -29,26 +29,34 @@ class FakeSolver:
         self.SN = np.zeros_like(self.S)
         self.S0 = np.zeros_like(self.S)
         self.new = None          # Stage-2 output while its parts are pending (phase 0 then addresses the NEW state)
+        self.ahead = False       # between AHEAD and S2_FINISH the pre-pass and halo phase 2 belong to the next step
+        self.prepass_done = False
+        self.dt_run = np.inf
         self.nx = self.S.shape[0]
         self.lo, self.hi = self.gl, self.nx - self.gr
         self.dt = 1.0
 
     # --- split step ---
     def step_begin(self):
-        self.prepass_done = False
+        pass
+
+    def _cur(self):
+        return self.new if self.ahead else self.S
 
     def step_prepass(self):
-        self.S0[:] = self.S                       # pre-overwrite values (SpecNode::S0)
+        S = self._cur()
+        self.S0[:] = S                            # pre-overwrite values (SpecNode::S0)
         for i in range(self.lo, self.hi):         # ordered chain: left already overwritten, right not yet
             if i == 0:
                 continue                          # global column 0 has no left neighbour
             r = self.S0[i + 1] if i + 1 < self.nx else self.S0[i]
-            self.S[i] = (self.S[i - 1] + r) * 0.5
+            S[i] = (S[i - 1] + r) * 0.5
         self.prepass_done = True
 
     def step_stage1(self):
         if not self.prepass_done:
             self.step_prepass()
+        self.prepass_done = False
         for i in range(self.lo, self.hi):
             l = self.S[i - 1] if i > 0 else self.S[i]
             r = self.S0[i + 1] if i + 1 < self.nx else self.S[i]
@@ -61,6 +69,7 @@ class FakeSolver:
             l_new = self.SN[i - 1] * 1.5 if i > 0 else self.SN[i] * 1.5     # left neighbour: recomputed NEW state (needs its SN)
             r_old = self.S[i + 1] if i + 1 < self.nx else self.S[i]           # right neighbour: after this step's pre-pass
             self.new[i] = self.SN[i] + 0.0625 * (r_old - l_new / 1.5)
+            self.dt_run = min(self.dt_run, float(1.0 / (1.0 + np.abs(self.new[i]).max())))   # CFL-like minimum, inside Stage 2
 
     def _edge_columns(self):
         return ([self.lo] if self.gl else []) + ([self.hi - 1] if self.gr else [])
@@ -71,10 +80,11 @@ class FakeSolver:
 
     def _s2_finish(self):
         self.S, self.new = self.new, None
-        self.dt = min(self.dt, float(1.0 / (1.0 + np.abs(self.S[self.lo:self.hi]).max())))
+        self.ahead = False
+        self.dt, self.dt_run = min(self.dt, self.dt_run), np.inf
 
     # --- the step in parts (cabi.Solver.step_part); lanes are streams on the GPU, nothing here ---
-    PREPASS, S1_PLAIN, S1_GENERAL, S1_FINISH, S2_INNER, S2_EDGE, S2_FINISH, PREPASS_LOCAL = 1, 2, 3, 4, 5, 6, 7, 8
+    PREPASS, S1_PLAIN, S1_GENERAL, S1_FINISH, S2_INNER, S2_EDGE, S2_FINISH, PREPASS_LOCAL, AHEAD = 1, 2, 3, 4, 5, 6, 7, 8, 9
 
     def step_part(self, part, lane=0, want_rms=1):
         if part == self.PREPASS:
@@ -88,6 +98,9 @@ class FakeSolver:
             self._s2_columns(self._edge_columns())
         elif part == self.S2_FINISH:
             self._s2_finish()
+        elif part == self.AHEAD:
+            assert self.new is not None
+            self.ahead = True
 
     def lane_fork(self):
         pass
@@ -110,7 +123,7 @@ class FakeSolver:
         elif phase == 1:
             b[:] = self.SN[col]
         else:
-            b[:] = self.S[col]
+            b[:] = self._cur()[col]
 
     def halo_unpack(self, side, phase, ptr, lane=0):
         col = 0 if side == 0 else self.nx - 1
@@ -120,7 +133,7 @@ class FakeSolver:
         elif phase == 1:
             self.SN[col] = b
         else:
-            self.S[col] = b
+            self._cur()[col] = b
 
     def dt_export(self, ptr):
         _view(ptr, 1)[0] = self.dt
