@@ -62,6 +62,7 @@ struct hf2d_gpu {
     // strip-sweep tiles (hf2d_stage2.cuh): TI columns x S2_WARPS strips of STRIP_ROWS rows
     int TI, n_sb, n_tx;
     int *d_tiles_plain, *d_tiles_gen; int n_plain, n_gen;
+    int* d_tiles_s1; int n_s1;      // Stage-1 list of the plain tiles, adjacent tiles merged (hf2d_io.inc)
     int n_plain_edge, n_gen_edge;   // the first n_*_edge tiles of each list touch a ghost column (X-slab seams): hf2d_gpu_step_part
     bool s2_pending;                // Stage-2 parts queued, planes not yet swapped (hf2d_gpu_step_part S2_FINISH does)
     int plain_ttc;                  // TurbType word of the plain tiles (-1: no plain kernel for this grid)
@@ -137,7 +138,7 @@ extern "C" int hf2d_gpu_create(const hf2d_cfg* cfg, int device, hf2d_gpu** out) 
     P.tab = h->d_tab; P.st = h->d_st;
     h->last_iter_cycle = cfg->last_iter;
     h->rms_every = cfg->NOutStep; h->prepass_done = false; h->timing = false; h->tn[0] = h->tn[1] = 0;
-    h->TI = 16; h->n_sb = h->n_tx = 0; h->d_tiles_plain = h->d_tiles_gen = nullptr; h->n_plain = h->n_gen = 0; h->n_plain_edge = h->n_gen_edge = 0; h->s2_pending = false; h->n_chains_local = 0; h->d_nlist_seam = nullptr; h->n_nlist_seam = 0; h->prepass_local_done = false; h->ahead = false; h->plain_ttc = -1;
+    h->TI = 16; h->n_sb = h->n_tx = 0; h->d_tiles_plain = h->d_tiles_gen = nullptr; h->n_plain = h->n_gen = 0; h->n_plain_edge = h->n_gen_edge = 0; h->d_tiles_s1 = nullptr; h->n_s1 = 0; h->s2_pending = false; h->n_chains_local = 0; h->d_nlist_seam = nullptr; h->n_nlist_seam = 0; h->prepass_local_done = false; h->ahead = false; h->plain_ttc = -1;
     *out = h;
     return HF2D_OK;
 }

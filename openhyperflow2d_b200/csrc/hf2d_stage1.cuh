@@ -192,6 +192,11 @@ __device__ __forceinline__ double ds_new(const Params& P, long long m, int k, in
 // equation is advanced with plain central differences, no special-node look-ups.
 #define STRIP_ROWS 31
 #define S1_WARPS 4
+#ifndef S1_MERGE
+#define S1_MERGE 1            // plain tiles merged per Stage-1 walk (<= 8: 3 bits of the list entry).  2 makes k_stage1<plain> itself
+                              // faster (0.76 -> 0.71 ms) but the step slower (2.91 -> 2.99 ms): its longer-lived blocks keep the general
+                              // tiles of the side stream waiting for SM slots, and Stage 2 waits for those (profiles/NOTES.md)
+#endif
 #define S1_THREADS (32 * S1_WARPS)
 
 template <class KC>
@@ -199,11 +204,12 @@ __global__ void __launch_bounds__(S1_THREADS) k_stage1(Params P, const int* __re
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int t_idx = blockIdx.x * S1_WARPS + warp;
     if (t_idx >= n_tiles) return;
-    const int tile = tiles[t_idx];
+    const int entry = tiles[t_idx];
+    const int tile = entry & 0x0fffffff, merged = (entry >> 28) + 1;     // Stage-1 plain list: up to S1_MERGE adjacent tiles per walk
     const int tx = tile / n_sb, sb = tile - tx * n_sb;
     const int j = sb * STRIP_ROWS + lane;
     if (lane >= STRIP_ROWS || j >= P.ny) return;
-    const int i0 = P.i_lo + tx * TI, i1 = min(i0 + TI, P.i_hi);
+    const int i0 = P.i_lo + tx * TI, i1 = min(i0 + TI * merged, P.i_hi);
     const long long ny = P.ny, N = P.N;
     const double dt = P.st->dt;
     const double dtdx = ddiv(dt, P.dx), dtdy = ddiv(dt, P.dy);                  // :843-844

@@ -117,6 +117,37 @@ def test_run_cycle_roundtrip_and_errors():
     s.close()
 
 
+@pytest.mark.parametrize("name", ["ns_keps_std_n8", "axi_reacting_euler_n10"])
+def test_staged_image_path_and_pinned_host(name, monkeypatch):
+    """The two host-image paths must agree: resident image in HBM (default) and the 256 MB stage used when the image does
+    not fit (forced here with HF2D_NO_RESIDENT_IMAGE=1); plus hf2d_gpu_pin_host / unpin_host on the caller's buffer."""
+    from openhyperflow2d_b200 import cabi
+    c = load_case(name)
+    out = []
+    for staged in (False, True):
+        if staged:
+            monkeypatch.setenv("HF2D_NO_RESIDENT_IMAGE", "1")
+        else:
+            monkeypatch.delenv("HF2D_NO_RESIDENT_IMAGE", raising=False)
+        J = np.array(c["state0"], copy=True)
+        s = cabi.Solver(c["cfg"], LAYOUT)
+        if staged:
+            assert cabi.lib().hf2d_gpu_pin_host(J.ctypes.data, J.nbytes) == 0
+        s.upload_aos(J, pinned=staged)
+        s.step(c["nsteps"])
+        s.download_aos(J, pinned=staged)
+        if staged:
+            assert cabi.lib().hf2d_gpu_unpin_host(J.ctypes.data) == 0
+        s.close()
+        out.append(J)
+    for f in out[0].dtype.names:
+        a, b = out[0][f], out[1][f]
+        assert ((a == b) | ((a != a) & (b != b))).all(), f"{name}: {f} differs between the resident and the staged image path"
+    for f in GPU_FIELDS:
+        a, b = np.asarray(out[1][f], float), np.asarray(c["stateN"][f], float)
+        assert rel_linf(a, b) <= REL_TOL, f
+
+
 @pytest.mark.parametrize("model,nsteps", [("keps", 6), ("sa", 2), ("laminar", 4), ("euler", 4)])
 def test_plain_tiles_match_oracle(model, nsteps):
     """A grid large enough to hold plain (unflagged interior) strip-sweep tiles: the specialised kernels and the
