@@ -172,8 +172,16 @@ k_stage2(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI,
             auto phaseA = [&](auto& dv, auto rms) {
                 double beta_min = OMIN(P.beta0, st.beta_scn);
                 const double bb = beta_min * beta_min;
+                // absent species (S[4..6] == 0 on every node of the warp's column: single-gas runs) take no residual and leave
+                // beta alone (res == false below): their 6 divisions + 3 square roots are skipped as ONE block, so that the
+                // other equations stay a single straight-line stretch
+                bool sp_any = false;
+#pragma unroll
+                for (int k = 4; k < 7; k++) sp_any |= upd && ld.S(k) != 0.;
+                sp_any = __any_sync(0xffffffffu, sp_any);
 #pragma unroll
                 for (int k = 0; k < NE_C; k++) {
+                    if (k >= 4 && k < 7 && !sp_any) continue;
                     const double so_k = valid_j ? ld.S(k) : 0., sn_k = valid_j ? ld.SN(k) : 0.;
                     const bool res = upd && so_k != 0.;
                     const double Tmp = res ? so_k : 1.0;
