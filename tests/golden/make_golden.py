@@ -50,7 +50,7 @@ def table(name, rows):
 def make_deck(name, *, nx=60, ny=40, dx=1e-3, dy=1e-3, problem=0, flow_type=0, turb=0, turb_ext=0, bff=4,
               adiabatic=1, alt_rms=1, nmax=2, tf=1000., k0=34., turb_reset=0, turb_start=0, cfl=0.1, beta=0.985,
               flows=None, bounds=None, contour=None, areas=None, single_bounds=(), monitor_index=5, delta_bl=1e-3,
-              sig_w=1.0, sig_f=1.0, beta_nrbc=0.25):
+              sig_w=1.0, sig_f=1.0, beta_nrbc=0.25, circles=(), rects=(), airfoils=(), cx_body=None):
     """Return deck text.  `flows`: list of dicts (Flow2D-n.*), `bounds`: list of (cond string, flow2d idx)."""
     L = [f"<start/{name}>"]
     d = lambda k, v: L.append(f"<data/{k}={v}>")
@@ -76,7 +76,24 @@ def make_deck(name, *, nx=60, ny=40, dx=1e-3, dy=1e-3, problem=0, flow_type=0, t
     for i, f in enumerate(flows, 1):
         for k, v in f.items():
             d(f"Flow2D-{i}.{k}", v)
-    d("NumRects", 0); d("NumCircles", 0); d("NumAirfoils", 0)
+    # solid bodies drawn by the reference's own rasterisers (deeps2d_core.cpp:4013-4282): no-slip contour nodes
+    # (NT_WNS_2D); the inside is filled by a solid Area seeded in it
+    d("NumRects", len(rects))
+    for i, r in enumerate(rects, 1):
+        for k in ("Xstart", "Ystart", "DX", "DY"):
+            d(f"Rect{i}.{k}", repr(r[k]))
+        d(f"Rect{i}.Flow2D", r.get("flow", 1)); d(f"Rect{i}.TurbulenceModel", turb)
+    d("NumCircles", len(circles))
+    for i, c in enumerate(circles, 1):
+        for k in ("Xstart", "Ystart", "X0", "Y0"):
+            d(f"Circle{i}.{k}", repr(c[k]))
+        d(f"Circle{i}.MaterialID", c.get("mat", 1)); d(f"Circle{i}.TurbulenceModel", turb); d(f"Circle{i}.Flow2D", c.get("flow", 1))
+    d("NumAirfoils", len(airfoils))
+    for i, a in enumerate(airfoils, 1):
+        d(f"Airfoil{i}.Xstart", repr(a["Xstart"])); d(f"Airfoil{i}.Ystart", repr(a["Ystart"])); d(f"Airfoil{i}.Type", 0)
+        d(f"Airfoil{i}.pp", repr(a["pp"])); d(f"Airfoil{i}.mm", repr(a["mm"])); d(f"Airfoil{i}.thick", repr(a["thick"]))
+        d(f"Airfoil{i}.scale", repr(a["scale"])); d(f"Airfoil{i}.attack_angle", repr(a["attack_angle"]))
+        d(f"Airfoil{i}.Flow2D", a.get("flow", 1)); d(f"Airfoil{i}.TurbulenceModel", turb)
     d("NumSingleBounds", len(single_bounds))
     for i, sb in enumerate(single_bounds, 1):
         L += table(f"SingleBound{i}.Points", sb["points"])
@@ -94,7 +111,9 @@ def make_deck(name, *, nx=60, ny=40, dx=1e-3, dy=1e-3, problem=0, flow_type=0, t
         d(f"Area{i}.Type", a["type"]); d(f"Area{i}.MaterialID", a.get("mat", 0))
         if a["type"] == 1:
             d(f"Area{i}.Flow2D", a["flow"]); d(f"Area{i}.TurbulenceModel", turb)
-    d("is_Cx_calc", 0); d("is_Cd_calc", 0); d("x_body", "0.0"); d("y_body", "0.0"); d("dx_body", "0.0"); d("dy_body", "0.0")
+    # airfoils need is_Cx_calc = 1: their constructor call reads Flow2D[Cx_Flow_Index - 1] (deeps2d_core.cpp:3972-3982,4284)
+    xb, yb, dxb, dyb = cx_body or (0.0, 0.0, 0.0, 0.0)
+    d("is_Cx_calc", 1 if cx_body else 0); d("is_Cd_calc", 0); d("x_body", repr(xb)); d("y_body", repr(yb)); d("dx_body", repr(dxb)); d("dy_body", repr(dyb))
     d("Cx_Flow_Index", 1); d("NumXCut", 0)
     L.append(f"<end/{name}>")
     return "\n".join(L) + "\n"
@@ -169,6 +188,41 @@ def cases():
     return C
 
 
+def geometry_cases():
+    """Bodies drawn by the reference's own rasterisers (BoundCircle2D, SolidBoundRect2D, SolidBoundAirfoil2D): staircase
+    no-slip walls with every corner type, in miniature of BASELINE configs 3 and 4.  Written to tests/golden/geometry/."""
+    G = {}
+    nx, ny, dx, dy = 96, 64, 1e-3, 1e-3
+    X, Y = nx * dx, ny * dy
+    box = [(0.0, Y), (X - 1e-5, Y), (X - 1e-5, 0.0), (0.0, 0.0)]
+    ke_b = [("NT_D0Y_2D, TCT_dkdy_NULL_2D, TCT_depsdy_NULL_2D", 1),
+            ("NT_D0X_2D, TCT_dkdx_NULL_2D, TCT_depsdx_NULL_2D, CT_NONREFLECTED_2D", 1),
+            ("NT_D0Y_2D, TCT_dkdy_NULL_2D, TCT_depsdy_NULL_2D", 1),
+            ("NT_FARFIELD_2D, TCT_k_CONST_2D, TCT_eps_CONST_2D", 1)]
+    ns_b = [("NT_D0Y_2D", 1), ("NT_D0X_2D, CT_NONREFLECTED_2D", 1), ("NT_D0Y_2D", 1), ("NT_FARFIELD_2D", 1)]
+    # three cylinders (BASELINE config 4 in miniature): radius 7, 6 and 5 cells, staggered
+    cyl = [(0.030, 0.032, 0.007), (0.058, 0.018, 0.006), (0.062, 0.047, 0.005)]
+    # (the body constructors fill their own inside with solid nodes and zero the velocity of the Flow2D they are given:
+    #  bodies get the still-air state, Flow2D-2)
+    circles = [{"X0": x0, "Y0": y0, "Xstart": x0 + r, "Ystart": y0, "flow": 2} for x0, y0, r in cyl]
+    c_areas = [{"seed": (3, 3), "type": 1, "flow": 1}]
+    G["cylinders_keps"] = dict(deck=dict(nx=nx, ny=ny, problem=1, turb=4, turb_ext=4, turb_reset=1, turb_start=1, adiabatic=0,
+                                         flows=[air(2.5), air()], bounds=ke_b, contour=box, areas=c_areas, circles=circles), steps=[8])
+    G["cylinders_laminar"] = dict(deck=dict(nx=nx, ny=ny, problem=1, turb=0, flows=[air(2.5), air()], bounds=ns_b, contour=box,
+                                            areas=c_areas, circles=circles), steps=[8])
+    # NACA 2412, zero incidence (BASELINE config 3 in miniature), chord 50 cells
+    foil = [{"Xstart": 0.020, "Ystart": 0.032, "pp": 0.4, "mm": 0.02, "thick": 0.12, "scale": 0.050, "attack_angle": 0.0, "flow": 2}]
+    f_areas = [{"seed": (3, 3), "type": 1, "flow": 1}]
+    G["airfoil_keps"] = dict(deck=dict(nx=nx, ny=ny, problem=1, turb=4, turb_ext=4, turb_reset=1, turb_start=1,
+                                       flows=[air(0.8), air()], bounds=ke_b, contour=box, areas=f_areas, airfoils=foil, cx_body=(0.015, 0.020, 0.060, 0.024)), steps=[8])
+    # solid rectangle (backward/forward facing steps), laminar, non-adiabatic wall
+    rect = [{"Xstart": 0.030, "Ystart": 0.020, "DX": 0.020, "DY": 0.012, "flow": 2}]
+    r_areas = [{"seed": (3, 3), "type": 1, "flow": 1}]
+    G["rect_laminar"] = dict(deck=dict(nx=nx, ny=ny, problem=1, turb=0, adiabatic=0, flows=[air(2.5), air()], bounds=ns_b, contour=box,
+                                       areas=r_areas, rects=rect), steps=[8])
+    return G
+
+
 def run_ref(deck_text, name, nstep, exit_time, wd):
     os.makedirs(wd, exist_ok=True)
     for f in os.listdir(wd):
@@ -186,7 +240,9 @@ def main(only=None):
     assert os.path.exists(DUMP), "build oracle/_ref first: make -C oracle ref"
     tmp = tempfile.mkdtemp(prefix="ohf_golden_")
     first = True
-    for cname, spec in cases().items():
+    os.makedirs(os.path.join(HERE, "geometry"), exist_ok=True)
+    todo = [(c, s, HERE) for c, s in cases().items()] + [(c, s, os.path.join(HERE, "geometry")) for c, s in geometry_cases().items()]
+    for cname, spec, outdir in todo:
         if only and cname not in only:
             continue
         runs = [(n, 1) for n in spec["steps"]]
@@ -203,16 +259,16 @@ def main(only=None):
             assert int(fin["last_iter"]) == nstep * ncyc, (tag, fin)
             if not os.path.exists(os.path.join(wd, "state0.hf2d")):
                 raise RuntimeError(open(os.path.join(wd, "log.txt")).read()[-2000:])
-            if first:
+            if first and outdir == HERE:
                 shutil.copy(os.path.join(wd, "layout.txt"), os.path.join(HERE, "layout.txt"))
                 first = False
             cfg = open(os.path.join(wd, "cfg.txt")).read()
             s0 = np.fromfile(os.path.join(wd, "state0.hf2d"), dtype=np.uint8)
             sN = np.fromfile(os.path.join(wd, cname + ".hf2d"), dtype=np.uint8)
             rms = open(os.path.join(wd, "RMS-" + cname + ".plt")).read()
-            np.savez_compressed(os.path.join(HERE, tag + ".npz"), state0=s0, stateN=sN, cfg=np.array(cfg), nsteps=nstep, ncycles=ncyc,
+            np.savez_compressed(os.path.join(outdir, tag + ".npz"), state0=s0, stateN=sN, cfg=np.array(cfg), nsteps=nstep, ncycles=ncyc,
                                 global_time=float(fin["GlobalTime"]), dt_final=float(fin["dt"]), rms_file=np.array(rms))
-            print(f"{tag}: {os.path.getsize(os.path.join(HERE, tag + '.npz')) / 1024:.0f} KiB  t={fin['GlobalTime']} dt={fin['dt']}")
+            print(f"{tag}: {os.path.getsize(os.path.join(outdir, tag + '.npz')) / 1024:.0f} KiB  t={fin['GlobalTime']} dt={fin['dt']}")
     shutil.rmtree(tmp, ignore_errors=True)
 
 

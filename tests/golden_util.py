@@ -15,8 +15,13 @@ def case_names():
     return sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "*.npz")))
 
 
+def geometry_case_names():
+    """Bodies drawn by the reference's own rasterisers (circles, rectangle, NACA airfoil): tests/golden/geometry/."""
+    return sorted("geometry/" + os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "geometry", "*.npz")))
+
+
 def load_case(name):
-    z = np.load(os.path.join(GOLDEN, name + ".npz"))
+    z = np.load(os.path.join(GOLDEN, *name.split("/")) + ".npz")
     cfg = config.parse_cfg(str(z["cfg"]))
     nx, ny = cfg["MaxX"], cfg["MaxY"]
     dt = aos.ref_dtype(LAYOUT)

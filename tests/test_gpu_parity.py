@@ -42,10 +42,13 @@ def rel_linf(a, b):
 
 @pytest.mark.parametrize("name", case_names())
 def test_gpu_matches_reference(name):
+    check_against_reference(name, exact=not name.startswith(TRANSCENDENTAL))
+
+
+def check_against_reference(name, exact):
     c = load_case(name)
     J, rep, t = run_gpu(c)
     ref = c["stateN"]
-    exact = not name.startswith(TRANSCENDENTAL)
     fields = GPU_FIELDS + (NS_FIELDS if c["cfg"]["ProblemType"] == 1 else [])
     if c["cfg"]["FT"] == 1:
         fields = fields + ["F"]
