@@ -223,6 +223,44 @@ def geometry_cases():
     return G
 
 
+def bc_cases():
+    """Boundary-condition branches of the step that no case above reaches: soft (second-derivative) outflow and far
+    boundaries, the wall-law wall, the second-derivative eps wall rewrites, the integral turbulence model, single Neumann
+    flags.  Same ramp duct as cases(); written to tests/golden/bc/."""
+    B = {}
+    nx, ny, dx, dy = 60, 40, 1e-3, 1e-3
+    geo = wedge_geometry(nx, ny, dx, dy, 0.02, 0.011)
+    areas = [{"seed": (3, 3), "type": 1, "flow": 1}, {"seed": (nx - 4, 2), "type": 0, "mat": 1}]
+    base = dict(flows=[air(2.5), air()], contour=geo, areas=areas)
+    # soft outflow (d2/dx2 = 0) and soft top (d2/dy2 = 0)
+    soft_e = [("NT_D2Y_2D", 1), ("NT_D2X_2D", 1), ("NT_D0Y_2D, CT_V_CONST_2D", 2), ("NT_D0Y_2D, CT_V_CONST_2D", 2), ("NT_FC_2D", 1)]
+    B["euler_soft"] = dict(deck=dict(problem=0, bounds=soft_e, bff=2, **base), steps=[8])
+    soft_k = [("NT_D2Y_2D, TCT_d2kdy2_NULL_2D, TCT_d2epsdy2_NULL_2D", 1),
+              ("NT_D2X_2D, TCT_d2kdx2_NULL_2D, TCT_d2epsdx2_NULL_2D", 1),
+              ("NT_WNS_2D, TCT_eps_mud2kdx2_WALL_2D", 2),
+              ("NT_WNS_2D, TCT_eps_mud2kdy2_WALL_2D", 2),
+              ("NT_FARFIELD_2D, TCT_k_CONST_2D, TCT_eps_CONST_2D", 1)]
+    B["ns_keps_soft_mud2k"] = dict(deck=dict(problem=1, turb=4, turb_ext=4, turb_reset=1, turb_start=1, bounds=soft_k, bff=3, **base), steps=[8])
+    # wall-law wall (slip velocity written into the momentum slot, SURVEY appendix A)
+    wl = [("NT_FARFIELD_2D, TCT_k_CONST_2D, TCT_eps_CONST_2D", 1),
+          ("NT_D0X_2D, TCT_dkdx_NULL_2D, TCT_depsdx_NULL_2D, CT_NONREFLECTED_2D", 1),
+          ("NT_WALL_LAW_2D, TCT_eps_Cmk2kXn_WALL_2D", 2),
+          ("NT_WALL_LAW_2D, TCT_eps_Cmk2kXn_WALL_2D", 2),
+          ("NT_FARFIELD_2D, TCT_k_CONST_2D, TCT_eps_CONST_2D", 1)]
+    B["ns_keps_wall_law"] = dict(deck=dict(problem=1, turb=4, turb_ext=4, turb_reset=1, turb_start=1, adiabatic=0, bounds=wl, **base), steps=[2])   # the reference itself aborts (Tg < 0) on step 3
+    wl_l = [("NT_FARFIELD_2D", 1), ("NT_D0X_2D", 1), ("NT_WALL_LAW_2D", 2), ("NT_WALL_LAW_2D", 2), ("NT_FARFIELD_2D", 1)]
+    B["ns_laminar_wall_law"] = dict(deck=dict(problem=1, turb=0, bounds=wl_l, bff=0, **base), steps=[2])
+    # integral model f(Re)
+    ns_b = [("NT_FARFIELD_2D", 1), ("NT_D0X_2D, CT_NONREFLECTED_2D", 1), ("NT_WNS_2D", 2), ("NT_D0Y_2D, CT_V_CONST_2D", 2), ("NT_FARFIELD_2D", 1)]
+    B["ns_integral"] = dict(deck=dict(problem=1, turb=1, turb_ext=0, turb_start=0, bounds=ns_b, bff=1, **base), steps=[8])
+    # single flags instead of the macro types: Neumann on some equations only, Dirichlet temperature on the wall
+    mixed = [("CT_dRhody_NULL_2D, CT_dTdy_NULL_2D, CT_dUdy_NULL_2D, CT_V_CONST_2D", 1),
+             ("CT_dRhodx_NULL_2D, CT_dUdx_NULL_2D, CT_d2Vdx2_NULL_2D, CT_d2Tdx2_NULL_2D, CT_dYdx_NULL_2D", 1),
+             ("NT_WNS_2D, CT_T_CONST_2D", 2), ("NT_D0Y_2D, CT_V_CONST_2D", 2), ("NT_FC_2D", 1)]
+    B["ns_laminar_mixed_flags"] = dict(deck=dict(problem=1, turb=0, bounds=mixed, **base), steps=[8])
+    return B
+
+
 def run_ref(deck_text, name, nstep, exit_time, wd):
     os.makedirs(wd, exist_ok=True)
     for f in os.listdir(wd):
@@ -241,7 +279,9 @@ def main(only=None):
     tmp = tempfile.mkdtemp(prefix="ohf_golden_")
     first = True
     os.makedirs(os.path.join(HERE, "geometry"), exist_ok=True)
-    todo = [(c, s, HERE) for c, s in cases().items()] + [(c, s, os.path.join(HERE, "geometry")) for c, s in geometry_cases().items()]
+    os.makedirs(os.path.join(HERE, "bc"), exist_ok=True)
+    todo = ([(c, s, HERE) for c, s in cases().items()] + [(c, s, os.path.join(HERE, "geometry")) for c, s in geometry_cases().items()]
+            + [(c, s, os.path.join(HERE, "bc")) for c, s in bc_cases().items()])
     for cname, spec, outdir in todo:
         if only and cname not in only:
             continue

@@ -20,6 +20,11 @@ def geometry_case_names():
     return sorted("geometry/" + os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "geometry", "*.npz")))
 
 
+def bc_case_names():
+    """Boundary-condition branches (soft BCs, wall law, eps wall rewrites, integral model, single flags): tests/golden/bc/."""
+    return sorted("bc/" + os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "bc", "*.npz")))
+
+
 def load_case(name):
     z = np.load(os.path.join(GOLDEN, *name.split("/")) + ".npz")
     cfg = config.parse_cfg(str(z["cfg"]))

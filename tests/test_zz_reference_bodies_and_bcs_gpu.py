@@ -6,11 +6,15 @@ solid rectangle (SolidBoundRect2D).  Their staircase no-slip contours hold every
 wall nodes with two solid neighbours, one-cell notches, diagonal steps -- which the straight ramp of the other golden
 cases and the synthetic grids of gridgen.py do not all contain.  The CPU oracle reproduces all four bit for bit
 (tests/test_oracle_vs_golden.py); the CUDA path is held to the same bar as in test_gpu_parity.py: bit-exact for the
-laminar cases, rel-L_inf <= 1e-10 where the k-eps wall rewrite calls pow()."""
+laminar cases, rel-L_inf <= 1e-10 where the k-eps wall rewrite calls pow().
+
+tests/golden/bc/*.npz (bc_cases()) do the same for boundary-condition branches of the step that the other cases do not
+reach: soft (second-derivative) outflow / far boundaries, the wall-law wall, the second-derivative eps wall rewrites, the
+integral turbulence model, single Neumann / Dirichlet flags instead of the macro node types."""
 import numpy as np
 import pytest
 
-from golden_util import LAYOUT, geometry_case_names, load_case
+from golden_util import LAYOUT, bc_case_names, geometry_case_names, load_case
 from test_gpu_parity import check_against_reference
 
 pytestmark = pytest.mark.gpu
@@ -22,7 +26,12 @@ def test_gpu_matches_reference_on_rasterised_bodies(name):
     check_against_reference(name, exact="keps" not in name)
 
 
-@pytest.mark.parametrize("name", ["geometry/cylinders_keps_n8", "geometry/airfoil_keps_n8"])
+@pytest.mark.parametrize("name", bc_case_names())
+def test_gpu_matches_reference_on_bc_branches(name):
+    check_against_reference(name, exact="keps" not in name)
+
+
+@pytest.mark.parametrize("name", ["geometry/cylinders_keps_n8", "geometry/airfoil_keps_n8", "bc/euler_soft_n8", "bc/ns_keps_soft_mud2k_n8"])
 def test_gpu_matches_oracle_stepwise_on_rasterised_bodies(name):
     """dt and the residual norms agree with the oracle after every single step (not only at the end of the cycle)."""
     import oracle_py as O
