@@ -786,3 +786,60 @@ int ohf_run_cycle(ohf_node* J, const ohf_cfg* g, unsigned last_iter, int nsteps,
     if (time_part) *time_part = tp;
     return 0;
 }
+
+/* ---- wall nodes and wall distance (init-time callers of the step: SURVEY section 8 f-3) -------------------------------
+ * Planar interface (x-major planes, node (i,j) at i*ny + j) so that the checker needs no record layout. */
+
+/* GetWallNodes, deeps2d_core.cpp:2081-2104: rows outermost (j), columns inside (i); non-solid nodes carrying the
+ * wall-law or the no-slip bit.  out_ij receives (i,j) pairs; returns the count (out_ij may be NULL to count only). */
+long ohf_get_wall_nodes(const uint64_t* ct, int nx, int ny, int* out_ij) {
+    long n = 0;
+    int i, j;
+    for (j = 0; j < ny; j++)
+        for (i = 0; i < nx; i++) {
+            uint64_t c = ct[(long)i * ny + j];
+            if ((c & CT_SOLID) == CT_SOLID) continue;
+            if ((c & CT_WALL_LAW) == CT_WALL_LAW || (c & CT_WALL_NO_SLIP) == CT_WALL_NO_SLIP) {
+                if (out_ij) { out_ij[2 * n] = i; out_ij[2 * n + 1] = j; }
+                n++;
+            }
+        }
+    return n;
+}
+
+/* SetMinDistanceToWall2D, deeps2d_core.cpp:4783-4832.  Every set, non-solid node: a node with Tg != 0 and p == 0 is
+ * turned into a solid one (status 2, CT updated in place as the reference does); every other one (status 1) folds the
+ * wall list IN ORDER: l = min(l, d); a wall that attains the running minimum -- ties included, so the LAST of several
+ * equidistant walls wins -- becomes (i_wall, j_wall); after every wall l is clamped from below to min(dx, dy).
+ * l_min / i_wall / j_wall of all other nodes (status 0) are left as they are. */
+void ohf_set_min_distance_to_wall(uint64_t* ct, const double* Tg, const double* p, int nx, int ny, double dx, double dy,
+                                  double x0, const int* wall_ij, long n_wall, double* l_min, int* i_wall, int* j_wall,
+                                  unsigned char* status) {
+    const double min_l_min = OMIN(dx, dy);
+    int i, j;
+    long ii;
+    for (i = 0; i < nx; i++)
+        for (j = 0; j < ny; j++) {
+            const long n = (long)i * ny + j;
+            if (status) status[n] = 0;
+            if (!((ct[n] & CT_NODE_IS_SET) == CT_NODE_IS_SET) || (ct[n] & CT_SOLID) == CT_SOLID) continue;
+            if (Tg[n] != 0 && p[n] == 0.) {
+                ct[n] |= CT_SOLID;
+                if (status) status[n] = 2;
+                continue;
+            }
+            if (status) status[n] = 1;
+            l_min[n] = OMAX((x0 + dx * (unsigned)nx), (dy * (unsigned)ny));
+            {
+                const double x = x0 + i * dx, y = j * dy;
+                for (ii = 0; ii < n_wall; ii++) {
+                    const unsigned iw = (unsigned)wall_ij[2 * ii], jw = (unsigned)wall_ij[2 * ii + 1];
+                    const double wx = iw * dx, wy = jw * dy;
+                    const double _l_min = sqrt((x - wx) * (x - wx) + (y - wy) * (y - wy));
+                    l_min[n] = OMIN(l_min[n], _l_min);
+                    if (l_min[n] == _l_min) { i_wall[n] = (int)iw; j_wall[n] = (int)jw; }
+                    l_min[n] = OMAX(min_l_min, l_min[n]);
+                }
+            }
+        }
+}

@@ -95,4 +95,12 @@ int ohf_run_cycle(ohf_node* J, const ohf_cfg* cfg, unsigned last_iter, int nstep
 #ifdef __cplusplus
 }
 #endif
+/* Wall nodes and wall distance (GetWallNodes, deeps2d_core.cpp:2081-2104; SetMinDistanceToWall2D, :4783-4832):
+ * planar, x-major.  Pinned by tests/test_wall_distance.py against l_min / i_wall / j_wall of the reference's own
+ * pre-step images (tests/golden: the reference runs both at start-up of every Navier-Stokes case). */
+long ohf_get_wall_nodes(const uint64_t* ct, int nx, int ny, int* out_ij);
+void ohf_set_min_distance_to_wall(uint64_t* ct, const double* Tg, const double* p, int nx, int ny, double dx, double dy,
+                                  double x0, const int* wall_ij, long n_wall, double* l_min, int* i_wall, int* j_wall,
+                                  unsigned char* status);
+
 #endif

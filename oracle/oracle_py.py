@@ -157,3 +157,34 @@ def run_cycle(nodes: np.ndarray, cfg: dict, last_iter: int, nsteps: int, dt_min:
     rep = StepReport()
     rc = lib().ohf_run_cycle(nodes.ctypes.data, C.byref(c), last_iter, nsteps, global_time, C.byref(dm), C.byref(rep), C.byref(tp))
     return rc, dm.value, rep, tp.value
+
+
+def wall_nodes(ct: np.ndarray) -> np.ndarray:
+    """GetWallNodes (deeps2d_core.cpp:2081-2104): (n, 2) int32 array of (i, j), rows outermost."""
+    ct = np.ascontiguousarray(ct, dtype=np.uint64)
+    nx, ny = ct.shape
+    L = lib()
+    L.ohf_get_wall_nodes.restype = C.c_long
+    L.ohf_get_wall_nodes.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+    n = L.ohf_get_wall_nodes(ct.ctypes.data, nx, ny, None)
+    out = np.zeros((max(n, 1), 2), dtype=np.int32)
+    L.ohf_get_wall_nodes(ct.ctypes.data, nx, ny, out.ctypes.data)
+    return out[:n]
+
+
+def set_min_distance_to_wall(ct, Tg, p, dx, dy, walls, l_min, i_wall, j_wall, x0=0.0):
+    """SetMinDistanceToWall2D (deeps2d_core.cpp:4783-4832) on x-major planes.  ct / l_min / i_wall / j_wall are updated in
+    place (contiguous uint64 / float64 / int32 / int32); returns the status plane (0 untouched, 1 computed, 2 made solid)."""
+    nx, ny = ct.shape
+    for a, t in ((ct, np.uint64), (l_min, np.float64), (i_wall, np.int32), (j_wall, np.int32)):
+        assert a.dtype == t and a.flags.c_contiguous and a.shape == (nx, ny)
+    Tg = np.ascontiguousarray(Tg, dtype=np.float64); p = np.ascontiguousarray(p, dtype=np.float64)
+    walls = np.ascontiguousarray(walls, dtype=np.int32)
+    status = np.zeros((nx, ny), dtype=np.uint8)
+    L = lib()
+    L.ohf_set_min_distance_to_wall.restype = None
+    L.ohf_set_min_distance_to_wall.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_double,
+                                               C.c_double, C.c_void_p, C.c_long, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.ohf_set_min_distance_to_wall(ct.ctypes.data, Tg.ctypes.data, p.ctypes.data, nx, ny, dx, dy, x0, walls.ctypes.data,
+                                   len(walls), l_min.ctypes.data, i_wall.ctypes.data, j_wall.ctypes.data, status.ctypes.data)
+    return status

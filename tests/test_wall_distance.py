@@ -1,0 +1,69 @@
+"""Wall nodes and wall distance (GetWallNodes, deeps2d_core.cpp:2081-2104; SetMinDistanceToWall2D, :4783-4832) -- the
+O(nodes x wall nodes) start-up pass in front of every Navier-Stokes run (hf2d_start.cpp:296-299).
+
+CPU part (here): the oracle's restatement is pinned against the reference itself -- every golden pre-step image
+(state0, written by the unmodified reference after its own start-up) carries the l_min / i_wall / j_wall members the
+reference computed; the oracle must rebuild them bit for bit from the flag words alone, the tie rule (the LAST of
+several equidistant wall nodes wins) and the clamp to min(dx, dy) included.
+
+GPU part (-m gpu): hf2d_gpu_set_min_distance_to_wall through the C ABI against the same images and the oracle."""
+import numpy as np
+import pytest
+
+import oracle_py as O
+from golden_util import LAYOUT, bc_case_names, case_names, geometry_case_names, load_case
+
+NS_CASES = [n for n in case_names() + geometry_case_names() + bc_case_names()
+            if not n.split("/")[-1].startswith(("euler", "axi_reacting_euler"))]
+
+
+def _planes(s):
+    return (np.ascontiguousarray(s["CT"], dtype=np.uint64), np.ascontiguousarray(s["Tg"]), np.ascontiguousarray(s["p"]))
+
+
+@pytest.mark.parametrize("name", NS_CASES)
+def test_oracle_rebuilds_reference_wall_distance(name):
+    c = load_case(name)
+    s, cfg = c["state0"], c["cfg"]
+    assert cfg["ProblemType"] == 1
+    ct, Tg, p = _planes(s)
+    walls = O.wall_nodes(ct)
+    l_min = np.full(ct.shape, -1.0); i_wall = np.full(ct.shape, -7, dtype=np.int32); j_wall = np.full(ct.shape, -7, dtype=np.int32)
+    ct_in = ct.copy()
+    status = O.set_min_distance_to_wall(ct, Tg, p, cfg["dx"], cfg["dy"], walls, l_min, i_wall, j_wall)
+    assert (ct == ct_in).all() and not (status == 2).any()        # no unfilled gas node in a finished start-up image
+    done = status == 1
+    set_gas = ((ct_in & 0x080000000) != 0) & ((ct_in & 0x040000000) == 0)
+    assert (done == set_gas).all() and done.sum() > 0
+    assert (l_min[done] == s["l_min"][done]).all()
+    if len(walls):
+        assert (i_wall[done] == s["i_wall"][done]).all() and (j_wall[done] == s["j_wall"][done]).all()
+    else:
+        assert (i_wall == -7).all() and (j_wall == -7).all()       # nothing to assign: members stay as they were
+    assert (l_min[~done] == -1.0).all() and (i_wall[~done] == -7).all()
+    if len(walls):
+        assert l_min[done].min() == min(cfg["dx"], cfg["dy"])      # the clamp: a wall node is its own nearest wall
+    else:                                                          # no wall in the deck (axisymmetric jet): domain extent
+        assert (l_min[done] == max(cfg["dx"] * cfg["MaxX"], cfg["dy"] * cfg["MaxY"])).all()
+
+
+def test_tie_rule_clamp_and_unfilled_nodes():
+    """4 x 3 grid, two wall nodes at equal distance from the middle node: the later one in GetWallNodes order wins."""
+    SET, SOLID, WNS = 0x080000000, 0x040000000, 0x04000000
+    ct = np.full((4, 3), SET, dtype=np.uint64)
+    ct[0, 1] |= WNS; ct[2, 1] |= WNS          # both at distance dx from (1,1)
+    ct[3, 0] = SET | SOLID | WNS               # solid: never a wall node, never visited
+    ct[3, 2] = 0                                # unset: not visited
+    Tg = np.full((4, 3), 300.0); p = np.full((4, 3), 1e5); p[1, 2] = 0.0   # (1,2): Tg != 0 and p == 0 -> made solid
+    walls = O.wall_nodes(ct)
+    assert walls.tolist() == [[0, 1], [2, 1]]
+    l_min = np.zeros((4, 3)); iw = np.full((4, 3), -1, dtype=np.int32); jw = np.full((4, 3), -1, dtype=np.int32)
+    st = O.set_min_distance_to_wall(ct, Tg, p, 0.5, 0.25, walls, l_min, iw, jw)
+    assert st[3, 0] == 0 and st[3, 2] == 0 and st[1, 2] == 2 and (ct[1, 2] & SOLID)
+    assert (iw[1, 1], jw[1, 1]) == (2, 1) and l_min[1, 1] == 0.5
+    assert (iw[0, 1], jw[0, 1]) == (0, 1) and l_min[0, 1] == 0.25     # distance 0 clamped to min(dx, dy)
+    assert (iw[2, 1], jw[2, 1]) == (2, 1)
+    # no wall nodes at all: l_min = max(x0 + dx*nx, dy*ny), no clamp, no wall assigned
+    l2 = np.zeros((4, 3)); iw2 = np.full((4, 3), -1, dtype=np.int32); jw2 = iw2.copy()
+    O.set_min_distance_to_wall(ct.copy(), Tg, p, 0.5, 0.25, walls[:0], l2, iw2, jw2, x0=1.0)
+    assert l2[1, 1] == 3.0 and iw2[1, 1] == -1
