@@ -190,6 +190,20 @@ int  hf2d_gpu_set_timing(hf2d_gpu* h, int enable);
 int  hf2d_gpu_get_timing(hf2d_gpu* h, double ms_mean[2], int count[2]);
 unsigned long long hf2d_gpu_launch_count(hf2d_gpu* h);      /* kernels launched through this handle so far */
 
+/* Wall distance of every set, non-solid node of the uploaded grid: replaces SetMinDistanceToWall2D(J, WallNodes, x0)
+ * (deeps2d_core.cpp:4783-4832; called at start-up of every Navier-Stokes run, hf2d_start.cpp:127, :171, :298 -- an
+ * O(nodes x wall nodes) loop on the host).  wall_ij = the reference's WallNodes array ((i,j) int pairs in GetWallNodes
+ * order, :2081-2104 -- the order decides ties: the LAST of several equidistant wall nodes wins), x0 = the sub-domain
+ * offset the reference passes (0 for the whole grid).  The device l_min plane the step reads is updated in place.
+ * Host outputs (each nx*ny, x-major, may be NULL):
+ *   status  0 = node not visited (unset or solid: its members stay as they are), 1 = computed,
+ *           2 = Tg != 0 and p == 0: the reference turns such a node into a solid one (SetCond2D(CT_SOLID_2D), :4797)
+ *               -- the caller does that on its record and uploads again before stepping;
+ *   l_min   FlowNode2D::l_min of status-1 nodes (other entries: the plane as uploaded, 0 without a plane);
+ *   i_wall, j_wall  the nearest wall node of status-1 nodes, -1 where the reference assigns none (member unchanged). */
+int  hf2d_gpu_set_min_distance_to_wall(hf2d_gpu* h, const int* wall_ij, int n_wall, double x0,
+                                       double* l_min, int* i_wall, int* j_wall, unsigned char* status);
+
 #ifdef __cplusplus
 }
 #endif

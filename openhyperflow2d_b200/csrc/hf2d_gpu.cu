@@ -161,3 +161,4 @@ extern "C" int hf2d_gpu_destroy(hf2d_gpu* h) {
 static bool plain_ttc_supported(int ttc);
 #include "hf2d_io.inc"
 #include "hf2d_step.inc"
+#include "hf2d_walldist.inc"

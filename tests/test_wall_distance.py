@@ -67,3 +67,94 @@ def test_tie_rule_clamp_and_unfilled_nodes():
     l2 = np.zeros((4, 3)); iw2 = np.full((4, 3), -1, dtype=np.int32); jw2 = iw2.copy()
     O.set_min_distance_to_wall(ct.copy(), Tg, p, 0.5, 0.25, walls[:0], l2, iw2, jw2, x0=1.0)
     assert l2[1, 1] == 3.0 and iw2[1, 1] == -1
+
+
+# ---- GPU part ----------------------------------------------------------------------------------------------------------
+
+def _gpu_wall_distance(c, J):
+    from openhyperflow2d_b200 import cabi
+    s = cabi.Solver(c["cfg"], LAYOUT)
+    s.upload_aos(J)
+    walls = O.wall_nodes(np.ascontiguousarray(J["CT"], dtype=np.uint64))
+    out = s.set_min_distance_to_wall(walls)
+    return s, walls, out
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", NS_CASES)
+def test_gpu_wall_distance_matches_reference(name):
+    """l_min / i_wall / j_wall of the reference's own start-up image, rebuilt on the GPU from the flag words: bit-exact."""
+    c = load_case(name)
+    ref = c["state0"]
+    J = np.array(ref, copy=True)
+    J["l_min"] = 123.0                                   # whatever the record held must not matter
+    s, walls, (l_min, i_wall, j_wall, status) = _gpu_wall_distance(c, J)
+    s.close()
+    ct = np.ascontiguousarray(ref["CT"], dtype=np.uint64)
+    set_gas = ((ct & 0x080000000) != 0) & ((ct & 0x040000000) == 0)
+    assert ((status == 1) == set_gas).all() and not (status == 2).any()
+    done = status == 1
+    assert (l_min[done] == ref["l_min"][done]).all()
+    assert (l_min[~done] == 123.0).all()                 # unvisited nodes: the plane as uploaded
+    if len(walls):
+        assert (i_wall[done] == ref["i_wall"][done]).all() and (j_wall[done] == ref["j_wall"][done]).all()
+    else:
+        assert (i_wall == -1).all() and (j_wall == -1).all()
+    assert (i_wall[~done] == -1).all()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["ns_prandtl_vd_n8", "ns_keps_std_n8", "geometry/cylinders_keps_n8"])
+def test_gpu_wall_distance_feeds_the_step(name):
+    """Start-up pass on the GPU, then the time steps: the image uploaded with a WRONG l_min ends where the reference
+    does, so the step reads the plane the pass wrote (mixing lengths and the eps wall value depend on l_min)."""
+    from test_gpu_parity import REL_TOL, rel_linf
+    c = load_case(name)
+    J = np.array(c["state0"], copy=True)
+    J["l_min"] = 0.5
+    s, _, _ = _gpu_wall_distance(c, J)
+    for _ in range(c["ncycles"]):
+        s.step(c["nsteps"])
+    s.download_aos(J)
+    s.close()
+    for f in ("S", "mu_t", "Tg"):
+        a, b = J[f], c["stateN"][f]
+        if a.ndim == 3:
+            for k in range(a.shape[-1]):
+                assert rel_linf(a[..., k], b[..., k]) <= REL_TOL, (name, f, k)
+        else:
+            assert rel_linf(a, b) <= REL_TOL, (name, f)
+
+
+@pytest.mark.gpu
+def test_gpu_wall_distance_ties_offsets_and_unfilled_nodes():
+    """Against the oracle on a grid built for the corner cases: x0 != 0 (sub-domain offset), a gas node with p == 0
+    (status 2), an empty wall list, more wall nodes than one shared-memory chunk (1024)."""
+    from openhyperflow2d_b200 import cabi
+    c = load_case("geometry/cylinders_laminar_n8")
+    J = np.array(c["state0"], copy=True)
+    J["p"][5, 7] = 0.0
+    for x0, cut in ((0.0, None), (0.0137, None), (0.0, 0)):
+        s = cabi.Solver(c["cfg"], LAYOUT)
+        s.upload_aos(J)
+        ct = np.ascontiguousarray(J["CT"], dtype=np.uint64)
+        walls = O.wall_nodes(ct)[:cut]
+        l_min, i_wall, j_wall, status = s.set_min_distance_to_wall(walls, x0=x0)
+        s.close()
+        lo = np.array(J["l_min"], copy=True); io = np.full(ct.shape, -1, dtype=np.int32); jo = io.copy()
+        so = O.set_min_distance_to_wall(ct.copy(), J["Tg"], J["p"], c["cfg"]["dx"], c["cfg"]["dy"], walls, lo, io, jo, x0=x0)
+        assert (status == so).all() and status[5, 7] == 2
+        assert (l_min == lo).all() and (i_wall == io).all() and (j_wall == jo).all()
+    # > 1 chunk of wall nodes: the list is the caller's -- every node of a 40 x 40 patch (1600 entries, rows outermost
+    # as GetWallNodes would list them), so nearly every node has several equidistant "walls"
+    J2 = np.array(c["state0"], copy=True)
+    s = cabi.Solver(c["cfg"], LAYOUT)
+    s.upload_aos(J2)
+    ct = np.ascontiguousarray(J2["CT"], dtype=np.uint64)
+    walls = np.array([(i, j) for j in range(2, 42) for i in range(2, 42)], dtype=np.int32)
+    assert len(walls) > 1024
+    l_min, i_wall, j_wall, status = s.set_min_distance_to_wall(walls)
+    s.close()
+    lo = np.array(J2["l_min"], copy=True); io = np.full(ct.shape, -1, dtype=np.int32); jo = io.copy()
+    so = O.set_min_distance_to_wall(ct.copy(), J2["Tg"], J2["p"], c["cfg"]["dx"], c["cfg"]["dy"], walls, lo, io, jo)
+    assert (status == so).all() and (l_min == lo).all() and (i_wall == io).all() and (j_wall == jo).all()
