@@ -111,7 +111,35 @@ void DEEPS2D_Run(ofstream* f_stream) {
     if (hf2d_gpu_create(&cfg, dev ? atoi(dev) : 0, &h)) die(f_stream, "create");
     // J lives as long as the run: page-lock it once so every per-cycle download runs at PCIe speed (optional)
     const int pinned = hf2d_gpu_pin_host(J->GetMatrixPtr(), (size_t)J->GetMatrixSize()) == 0;
+    // Optional second seam (INTEGRATION.md, HF2D_GPU_WALL_DISTANCE=1): SetMinDistanceToWall2D on the GPU.  main() has
+    // already run the host version by the time DEEPS2D_Run is called (hf2d_start.cpp:298) -- a maintainer would drop that
+    // call -- so its results are wiped from J first: what the step and the swap file see is what the GPU computed.
+    const bool gpu_wall_distance = getenv("HF2D_GPU_WALL_DISTANCE") && atoi(getenv("HF2D_GPU_WALL_DISTANCE")) &&
+                                   ProblemType == SM_NS && WallNodes;
+    if (gpu_wall_distance) {
+        for (int i = 0; i < MaxX; i++) for (int j = 0; j < MaxY; j++) {
+            Node& nd = J->GetValue(i, j);
+            if (nd.isCond2D(CT_NODE_IS_SET_2D) && !nd.isCond2D(CT_SOLID_2D)) { nd.l_min = -1.; nd.i_wall = -1; nd.j_wall = -1; }
+        }
+    }
     if (hf2d_gpu_upload_aos(h, J->GetMatrixPtr(), &lay, pinned)) die(f_stream, "upload");
+    if (gpu_wall_distance) {
+        const size_t N = (size_t)MaxX * MaxY;
+        double* wl = new double[N]; int* wi = new int[N]; int* wj = new int[N]; unsigned char* ws = new unsigned char[N];
+        // XY<int> is two ints (utl/umatrix2d.hpp:44-65): the array is the (i,j) pair list in GetWallNodes order
+        if (hf2d_gpu_set_min_distance_to_wall(h, (const int*)WallNodes->GetArrayPtr(), (int)WallNodes->GetNumElements(), 0.0,
+                                              wl, wi, wj, ws)) die(f_stream, "wall distance");
+        long n_solid = 0;
+        for (int i = 0; i < MaxX; i++) for (int j = 0; j < MaxY; j++) {
+            const size_t n = (size_t)i * MaxY + j;
+            Node& nd = J->GetValue(i, j);
+            if (ws[n] == 1) { nd.l_min = wl[n]; if (wi[n] >= 0) { nd.i_wall = wi[n]; nd.j_wall = wj[n]; } }
+            else if (ws[n] == 2) { nd.SetCond2D(CT_SOLID_2D); n_solid++; }        // deeps2d_core.cpp:4797
+        }
+        delete[] wl; delete[] wi; delete[] wj; delete[] ws;
+        if (n_solid && hf2d_gpu_upload_aos(h, J->GetMatrixPtr(), &lay, pinned)) die(f_stream, "upload");
+        *f_stream << "hf2d_gpu: wall distance of " << WallNodes->GetNumElements() << " wall nodes on the GPU\n" << flush;
+    }
     *f_stream << "hf2d_gpu: DEEPS2D time loop on the GPU (" << MaxX << "x" << MaxY << " nodes)\n" << flush;
 
     I = 0; isRun = 1;

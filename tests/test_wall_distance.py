@@ -158,3 +158,31 @@ def test_gpu_wall_distance_ties_offsets_and_unfilled_nodes():
     lo = np.array(J2["l_min"], copy=True); io = np.full(ct.shape, -1, dtype=np.int32); jo = io.copy()
     so = O.set_min_distance_to_wall(ct.copy(), J2["Tg"], J2["p"], c["cfg"]["dx"], c["cfg"]["dy"], walls, lo, io, jo)
     assert (status == so).all() and (l_min == lo).all() and (i_wall == io).all() and (j_wall == jo).all()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case,exact", [("ns_laminar", True), ("ns_keps_std", False)])
+def test_reference_program_with_gpu_wall_distance(case, exact, tmp_path, monkeypatch):
+    """The second seam in the reference PROGRAM: oracle/_ref/ohf_gpu with HF2D_GPU_WALL_DISTANCE=1 wipes the l_min /
+    i_wall / j_wall its own start-up computed, rebuilds them on the GPU and steps on those; the swap file it leaves
+    must carry the same three members as the unmodified program's, and the same flow field."""
+    import os
+    import test_shim_dropin as D
+    if not (os.path.exists(D.REF) and os.path.exists(D.GPU)):
+        pytest.skip("oracle/_ref not built (make -C oracle ref)")
+    deck = D._deck(case, 6, 2, 3e-7)
+    Jr, rms_r, _ = D._run(D.REF, deck, case, str(tmp_path / "ref"))
+    monkeypatch.setenv("HF2D_GPU_WALL_DISTANCE", "1")
+    Jg, rms_g, out = D._run(D.GPU, deck, case, str(tmp_path / "gpu"))
+    assert "wall nodes on the GPU" in out
+    assert len(rms_g) == len(rms_r)
+    for f in ("l_min", "i_wall", "j_wall", "CT"):
+        assert (Jg[f] == Jr[f]).all(), f
+    assert (Jr["l_min"] > 0).any()
+    for f in ("S", "Tg", "mu_t"):
+        a, b = Jg[f], Jr[f]
+        if exact:
+            assert ((a == b) | ((a != a) & (b != b))).all(), f
+        else:
+            scale = max(float(np.abs(b).max()), 1e-300)
+            assert float(np.abs(a - b).max()) / scale <= 1e-10, f
