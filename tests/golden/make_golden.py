@@ -261,9 +261,21 @@ def bc_cases():
     return B
 
 
-def run_ref(deck_text, name, nstep, exit_time, wd):
+def restart_cases():
+    """Runs RESTARTED from the swap file of an earlier run of the same deck (`restart_after` steps): the reference's
+    start-up then computes y_plus from real wall gradients (Recalc_y_plus, hf2d_start.cpp:299) -- in a fresh run they are
+    zero and y_plus = 0 everywhere -- so these are the cases in which the y+ damping functions (van Driest, Chien, JL,
+    LSY) and the restored-wall-node start-up path see non-trivial input.  Written to tests/golden/restart/."""
+    C = cases()
+    R = {}
+    for name in ("ns_prandtl_vd", "ns_keps_std", "ns_keps_chien", "ns_keps_jl", "ns_keps_lsy", "ns_laminar"):
+        R[name] = dict(deck=C[name]["deck"], steps=[6], restart_after=12)
+    return R
+
+
+def run_ref(deck_text, name, nstep, exit_time, wd, clean=True):
     os.makedirs(wd, exist_ok=True)
-    for f in os.listdir(wd):
+    for f in os.listdir(wd) if clean else ():
         os.remove(os.path.join(wd, f))
     with open(os.path.join(wd, name + ".dat"), "w") as f:
         f.write(deck_text)
@@ -281,10 +293,14 @@ def main(only=None):
     os.makedirs(os.path.join(HERE, "geometry"), exist_ok=True)
     os.makedirs(os.path.join(HERE, "bc"), exist_ok=True)
     todo = ([(c, s, HERE) for c, s in cases().items()] + [(c, s, os.path.join(HERE, "geometry")) for c, s in geometry_cases().items()]
-            + [(c, s, os.path.join(HERE, "bc")) for c, s in bc_cases().items()])
+            + [(c, s, os.path.join(HERE, "bc")) for c, s in bc_cases().items()]
+            + [(c, s, os.path.join(HERE, "restart")) for c, s in restart_cases().items()])
+    os.makedirs(os.path.join(HERE, "restart"), exist_ok=True)
     for cname, spec, outdir in todo:
-        if only and cname not in only:
+        if only and cname not in only and os.path.basename(outdir) + "/" + cname not in only:
             continue
+        if only and outdir != HERE and cname in cases() and os.path.basename(outdir) + "/" + cname not in only:
+            continue            # a restart case shares its name with the fresh one: ask for it as restart/<name>
         runs = [(n, 1) for n in spec["steps"]]
         if spec.get("two_cycle"):
             runs.append((spec["two_cycle"], 2))
@@ -292,7 +308,13 @@ def main(only=None):
             tag = f"{cname}_n{nstep}" + ("x2" if ncyc == 2 else "")
             deck = make_deck(cname, **spec["deck"])
             wd = os.path.join(tmp, tag)
-            fin = run_ref(deck, cname, nstep, 1e-300, wd)
+            if spec.get("restart_after"):
+                tag = f"{cname}_r{spec['restart_after']}_n{nstep}"
+                run_ref(deck, cname, spec["restart_after"], 1e-300, wd)       # leaves <case>.hf2d, the swap file
+                fin = run_ref(deck, cname, nstep, 1e-300, wd, clean=False)    # "Use old 2D-swap file"
+                assert "Use old 2D-swap file" in open(os.path.join(wd, "log.txt")).read()
+            else:
+                fin = run_ref(deck, cname, nstep, 1e-300, wd)
             if ncyc == 2:  # second pass: stop after the 2nd cycle (GlobalTime after 1 cycle < T <= after 2)
                 t1 = float(fin["GlobalTime"])
                 fin = run_ref(deck, cname, nstep, 1.5 * t1, wd)

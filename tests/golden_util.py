@@ -25,6 +25,11 @@ def bc_case_names():
     return sorted("bc/" + os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "bc", "*.npz")))
 
 
+def restart_case_names():
+    """Runs restarted from a swap file: non-zero y_plus, restored wall nodes (tests/golden/restart/)."""
+    return sorted("restart/" + os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "restart", "*.npz")))
+
+
 def load_case(name):
     z = np.load(os.path.join(GOLDEN, *name.split("/")) + ".npz")
     cfg = config.parse_cfg(str(z["cfg"]))

@@ -11,9 +11,9 @@ import numpy as np
 import pytest
 
 import oracle_py as O
-from golden_util import LAYOUT, bc_case_names, case_names, geometry_case_names, load_case
+from golden_util import LAYOUT, bc_case_names, case_names, geometry_case_names, load_case, restart_case_names
 
-NS_CASES = [n for n in case_names() + geometry_case_names() + bc_case_names()
+NS_CASES = [n for n in case_names() + geometry_case_names() + bc_case_names() + restart_case_names()
             if not n.split("/")[-1].startswith(("euler", "axi_reacting_euler"))]
 
 

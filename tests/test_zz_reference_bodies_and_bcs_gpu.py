@@ -10,11 +10,15 @@ laminar cases, rel-L_inf <= 1e-10 where the k-eps wall rewrite calls pow().
 
 tests/golden/bc/*.npz (bc_cases()) do the same for boundary-condition branches of the step that the other cases do not
 reach: soft (second-derivative) outflow / far boundaries, the wall-law wall, the second-derivative eps wall rewrites, the
-integral turbulence model, single Neumann / Dirichlet flags instead of the macro node types."""
+integral turbulence model, single Neumann / Dirichlet flags instead of the macro node types.
+
+tests/golden/restart/*.npz (restart_cases()) are runs RESTARTED from the swap file of an earlier run: the reference's
+start-up then derives y_plus from real wall gradients (it is 0 everywhere in a fresh run), so these are the cases in
+which the y+ damping functions (van Driest exp, Chien / JL / LSY) see non-trivial input."""
 import numpy as np
 import pytest
 
-from golden_util import LAYOUT, bc_case_names, geometry_case_names, load_case
+from golden_util import LAYOUT, bc_case_names, geometry_case_names, load_case, restart_case_names
 from test_gpu_parity import check_against_reference
 
 pytestmark = pytest.mark.gpu
@@ -26,12 +30,20 @@ def test_gpu_matches_reference_on_rasterised_bodies(name):
     check_against_reference(name, exact="keps" not in name)
 
 
+@pytest.mark.parametrize("name", restart_case_names())
+def test_gpu_matches_reference_after_restart(name):
+    c = load_case(name)
+    assert float(np.abs(c["state0"]["y_plus"]).max()) > 1.0        # the point of these cases
+    check_against_reference(name, exact="laminar" in name)
+
+
 @pytest.mark.parametrize("name", bc_case_names())
 def test_gpu_matches_reference_on_bc_branches(name):
     check_against_reference(name, exact="keps" not in name)
 
 
-@pytest.mark.parametrize("name", ["geometry/cylinders_keps_n8", "geometry/airfoil_keps_n8", "bc/euler_soft_n8", "bc/ns_keps_soft_mud2k_n8"])
+@pytest.mark.parametrize("name", ["geometry/cylinders_keps_n8", "geometry/airfoil_keps_n8", "bc/euler_soft_n8", "bc/ns_keps_soft_mud2k_n8",
+                                  "restart/ns_keps_chien_r12_n6", "restart/ns_prandtl_vd_r12_n6"])
 def test_gpu_matches_oracle_stepwise_on_rasterised_bodies(name):
     """dt and the residual norms agree with the oracle after every single step (not only at the end of the cycle)."""
     import oracle_py as O
