@@ -350,6 +350,12 @@ k_stage2(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI,
                         }
                     }
                     g.dTdx = (nR.Tg - nL.Tg) * dxn; g.dTdy = (nU.Tg - nD.Tg) * dym;
+                    // the only gradients anything reads after the step: dUdy, dVdx of the wall nodes (Recalc_y_plus when a
+                    // run is restarted from the swap file, deeps2d_core.cpp:2364-2386) -> kept in the special-node table for
+                    // hf2d_gpu_download_aos; these two slots are read back by nobody on an active node
+                    if constexpr (!KC::plain) {
+                        if (sp && (is_set(ct, CT_WALL_NO_SLIP) || is_set(ct, CT_WALL_LAW))) { sp->grad[9] = g.dUdy; sp->grad[10] = g.dVdx; }
+                    }
                 } else {   // NT_FC node: FillNode2D runs on the gradients stored in the record (never refreshed)
                     for (int q = 0; q < 4; q++) { g.droYdx[q] = sp->grad[q]; g.droYdy[q] = sp->grad[4 + q]; }
                     g.dUdx = sp->grad[8]; g.dUdy = sp->grad[9]; g.dVdx = sp->grad[10]; g.dVdy = sp->grad[11];

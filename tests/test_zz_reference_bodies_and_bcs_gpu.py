@@ -64,3 +64,28 @@ def test_gpu_matches_oracle_stepwise_on_rasterised_bodies(name):
         np.testing.assert_allclose(list(grep.sum_RMS), list(orep.sum_RMS), rtol=1e-9, atol=1e-300)
         np.testing.assert_allclose(list(grep.DD_max), list(orep.DD_max), rtol=1e-9, atol=1e-300)
     s.close()
+
+
+@pytest.mark.parametrize("name", ["ns_laminar_n8", "ns_keps_std_n8", "ns_keps_std_n4x2", "geometry/cylinders_keps_n8",
+                                  "geometry/airfoil_keps_n8", "geometry/rect_laminar_n8", "restart/ns_keps_chien_r12_n6"])
+def test_wall_gradients_come_back_for_a_restart(name):
+    """dUdy, dVdx of the wall nodes are the two gradient members something reads after the step: the start-up of a run
+    restarted from the swap file derives y_plus from them (Recalc_y_plus, deeps2d_core.cpp:2364-2386).  Stage 2 keeps
+    them in the boundary table and hf2d_gpu_download_aos writes them into the records; every other gradient member is an
+    intermediate and comes back as uploaded."""
+    from test_gpu_parity import REL_TOL, rel_linf, run_gpu
+    c = load_case(name)
+    J, _, _ = run_gpu(c)
+    ref = c["stateN"]
+    ct = np.ascontiguousarray(ref["CT"], dtype=np.uint64)
+    wall = ((ct & 0x040000000) == 0) & (((ct & 0x04000000) != 0) | ((ct & 0x08000000) != 0))
+    assert wall.sum() > 0
+    for f in ("dUdy", "dVdx"):
+        a, b = J[f][wall], ref[f][wall]
+        assert np.abs(b).max() > 0, (name, f)
+        if "laminar" in name:
+            assert (a == b).all(), (name, f, int((a != b).sum()))
+        else:
+            assert rel_linf(a, b) <= REL_TOL, (name, f, rel_linf(a, b))
+        off = ~wall
+        assert (J[f][off] == c["state0"][f][off]).all()      # everything else: as uploaded
