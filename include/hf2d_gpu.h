@@ -190,6 +190,12 @@ int  hf2d_gpu_set_timing(hf2d_gpu* h, int enable);
 int  hf2d_gpu_get_timing(hf2d_gpu* h, double ms_mean[2], int count[2]);
 unsigned long long hf2d_gpu_launch_count(hf2d_gpu* h);      /* kernels launched through this handle so far */
 
+/* GlobalTime of the running output cycle.  The reference stamps it on every swept node (FlowNode2D::time,
+ * deeps2d_core.cpp:867) and a run restarted from the swap file takes its GlobalTime from node (0,0) (:4618-4621).
+ * Optional: once set, hf2d_gpu_download_aos writes it into the `time` member of the swept nodes; never set, that member
+ * comes back as uploaded.  Call it before the download of each cycle with the cycle's GlobalTime (before += CurrentTimePart). */
+int  hf2d_gpu_set_global_time(hf2d_gpu* h, double global_time);
+
 /* Wall distance of every set, non-solid node of the uploaded grid: replaces SetMinDistanceToWall2D(J, WallNodes, x0)
  * (deeps2d_core.cpp:4783-4832; called at start-up of every Navier-Stokes run, hf2d_start.cpp:127, :171, :298 -- an
  * O(nodes x wall nodes) loop on the host).  wall_ij = the reference's WallNodes array ((i,j) int pairs in GetWallNodes

@@ -69,6 +69,7 @@ struct hf2d_gpu {
     // optional per-kernel timing of the two plain-tile launches (bench.py roofline): event pairs on the main stream
     bool timing; std::vector<cudaEvent_t> tev[2][2]; int tn[2];
     bool prepass_done;              // hf2d_gpu_step_prepass already ran for the current step
+    double global_time; bool have_global_time;   // GlobalTime of the running cycle (hf2d_gpu_set_global_time): FlowNode2D::time at download
     int rms_every;                  // residual norms are reduced on steps with iter % rms_every == 0 and on the last step of a call
 };
 

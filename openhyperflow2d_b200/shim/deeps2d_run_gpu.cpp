@@ -203,6 +203,7 @@ void DEEPS2D_Run(ofstream* f_stream) {
             }
         }
         // --- cycle end (deeps2d_core.cpp:1762-1849): grid back to the host image, then the reference's own writers ---
+        hf2d_gpu_set_global_time(h, GlobalTime);            // FlowNode2D::time of the swept nodes (:867): still the cycle's start value
         if (hf2d_gpu_download_aos(h, J->GetMatrixPtr(), &lay, pinned)) die(f_stream, "download");
         if (XCutArray->GetNumElements() > 0) {
             for (int i_xcut = 0; i_xcut < (int)XCutArray->GetNumElements(); i_xcut++) {

@@ -136,3 +136,27 @@ def test_restart_chain_through_the_reference_program(case, exact, tmp_path):
             assert float(np.abs(a - b).max()) / scale <= 1e-10, (case, f)
     for f in ("CT", "TurbType", "i_wall", "j_wall"):
         assert (Jg[f] == Jr[f]).all(), (case, f)
+
+
+@pytest.mark.parametrize("name", ["ns_laminar_n4x2", "ns_keps_std_n4x2"])
+def test_time_member_of_swept_nodes(name):
+    """FlowNode2D::time: the reference stamps the running cycle's GlobalTime on every swept node (deeps2d_core.cpp:867)
+    and a restarted run reads its GlobalTime from node (0,0) (:4618-4621).  Two-cycle golden runs: after the second
+    cycle the member holds the GlobalTime reached at the end of the first."""
+    from openhyperflow2d_b200 import cabi
+    c = load_case(name)
+    assert c["ncycles"] == 2
+    J = np.array(c["state0"], copy=True)
+    s = cabi.Solver(c["cfg"], LAYOUT)
+    s.upload_aos(J)
+    t = c["cfg"].get("GlobalTime", 0.0)
+    for _ in range(c["ncycles"]):
+        rep = s.step(c["nsteps"])
+        t_cycle_start, t = t, t + rep.time_part
+    s.set_global_time(t_cycle_start)
+    s.download_aos(J)
+    s.close()
+    ref = c["stateN"]["time"]
+    assert float(ref.max()) > 0 and t_cycle_start > 0
+    assert np.allclose(J["time"], ref, rtol=1e-12, atol=0.0)
+    assert ((J["time"] != 0) == (ref != 0)).all()              # exactly the swept nodes
