@@ -39,7 +39,7 @@ def test_gpu_matches_reference_after_restart(name):
 
 @pytest.mark.parametrize("name", bc_case_names())
 def test_gpu_matches_reference_on_bc_branches(name):
-    check_against_reference(name, exact="keps" not in name)
+    check_against_reference(name, exact=not any(t in name for t in ("keps", "ns_sa")))     # pow() / exp() closures
 
 
 @pytest.mark.parametrize("name", ["geometry/cylinders_keps_n8", "geometry/airfoil_keps_n8", "bc/euler_soft_n8", "bc/ns_keps_soft_mud2k_n8",
