@@ -843,3 +843,25 @@ void ohf_set_min_distance_to_wall(uint64_t* ct, const double* Tg, const double* 
             }
         }
 }
+
+/* Recalc_y_plus, deeps2d_core.cpp:2364-2386 (the serial build's variant; start-up, hf2d_start.cpp:299, and once per
+ * output cycle on rank 0 of the MPI build, :1723-1726): y+ of every set, non-solid node from the friction velocity of
+ * ITS nearest wall node (i_wall, j_wall) and -- as the reference has it -- the grid step min(dx, dy), not l_min. */
+void ohf_recalc_y_plus(const uint64_t* ct, int nx, int ny, double dx, double dy, const int* i_wall, const int* j_wall,
+                       const double* dUdy, const double* dVdx, const double* mu, const double* rho, double* y_plus) {
+    int i, j;
+    for (i = 0; i < nx; i++)
+        for (j = 0; j < ny; j++) {
+            const long n = (long)i * ny + j;
+            if ((ct[n] & CT_NODE_IS_SET) == CT_NODE_IS_SET && !((ct[n] & CT_SOLID) == CT_SOLID)) {
+                const long w = (long)(unsigned)i_wall[n] * ny + (unsigned)j_wall[n];
+                const double tau_w = (fabs(dUdy[w]) + fabs(dVdx[w])) * mu[w];
+                if (rho[w] > 0.0 && tau_w > 0.0) {
+                    const double U_w = sqrt(tau_w / rho[w] + 1e-30);
+                    y_plus[n] = fabs(U_w * OMIN(dx, dy) * rho[n] / mu[n]);
+                } else {
+                    y_plus[n] = 0.0;
+                }
+            }
+        }
+}

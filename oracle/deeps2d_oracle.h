@@ -103,4 +103,9 @@ void ohf_set_min_distance_to_wall(uint64_t* ct, const double* Tg, const double* 
                                   double x0, const int* wall_ij, long n_wall, double* l_min, int* i_wall, int* j_wall,
                                   unsigned char* status);
 
+/* Recalc_y_plus (deeps2d_core.cpp:2364-2386), planar; pinned by tests/test_wall_distance.py against the y_plus member of
+ * the reference's start-up images of RESTARTED runs (tests/golden/restart: the only ones with non-zero wall gradients). */
+void ohf_recalc_y_plus(const uint64_t* ct, int nx, int ny, double dx, double dy, const int* i_wall, const int* j_wall,
+                       const double* dUdy, const double* dVdx, const double* mu, const double* rho, double* y_plus);
+
 #endif

@@ -188,3 +188,17 @@ def set_min_distance_to_wall(ct, Tg, p, dx, dy, walls, l_min, i_wall, j_wall, x0
     L.ohf_set_min_distance_to_wall(ct.ctypes.data, Tg.ctypes.data, p.ctypes.data, nx, ny, dx, dy, x0, walls.ctypes.data,
                                    len(walls), l_min.ctypes.data, i_wall.ctypes.data, j_wall.ctypes.data, status.ctypes.data)
     return status
+
+
+def recalc_y_plus(ct, dx, dy, i_wall, j_wall, dUdy, dVdx, mu, rho, y_plus):
+    """Recalc_y_plus (deeps2d_core.cpp:2364-2386) on x-major planes; y_plus (float64, contiguous) is updated in place."""
+    ct = np.ascontiguousarray(ct, dtype=np.uint64)
+    nx, ny = ct.shape
+    a = [np.ascontiguousarray(v, dtype=t) for v, t in ((i_wall, np.int32), (j_wall, np.int32), (dUdy, np.float64),
+                                                       (dVdx, np.float64), (mu, np.float64), (rho, np.float64))]
+    assert y_plus.dtype == np.float64 and y_plus.flags.c_contiguous and y_plus.shape == (nx, ny)
+    L = lib()
+    L.ohf_recalc_y_plus.restype = None
+    L.ohf_recalc_y_plus.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_double] + [C.c_void_p] * 7
+    L.ohf_recalc_y_plus(ct.ctypes.data, nx, ny, dx, dy, *[v.ctypes.data for v in a], y_plus.ctypes.data)
+    return y_plus

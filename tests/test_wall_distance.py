@@ -69,6 +69,24 @@ def test_tie_rule_clamp_and_unfilled_nodes():
     assert l2[1, 1] == 3.0 and iw2[1, 1] == -1
 
 
+@pytest.mark.parametrize("name", restart_case_names() + ["ns_keps_std_n8", "geometry/cylinders_keps_n8"])
+def test_oracle_rebuilds_reference_y_plus(name):
+    """Recalc_y_plus (deeps2d_core.cpp:2364-2386) against the y_plus member the reference's own start-up left in the
+    image: non-trivial for restarted runs (wall gradients of the previous run), identically 0 for fresh ones."""
+    c = load_case(name)
+    s, cfg = c["state0"], c["cfg"]
+    yp = np.full(s["y_plus"].shape, -3.0)
+    O.recalc_y_plus(s["CT"], cfg["dx"], cfg["dy"], s["i_wall"], s["j_wall"], s["dUdy"], s["dVdx"], s["mu"], s["S"][..., 0], yp)
+    ct = np.ascontiguousarray(s["CT"], dtype=np.uint64)
+    done = ((ct & 0x080000000) != 0) & ((ct & 0x040000000) == 0)
+    assert (yp[done] == s["y_plus"][done]).all()
+    assert (yp[~done] == -3.0).all()
+    if name.startswith("restart/"):
+        assert float(s["y_plus"].max()) > 100.0
+    else:
+        assert float(np.abs(s["y_plus"]).max()) == 0.0
+
+
 # ---- GPU part ----------------------------------------------------------------------------------------------------------
 
 def _gpu_wall_distance(c, J):
