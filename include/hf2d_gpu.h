@@ -210,6 +210,15 @@ int  hf2d_gpu_set_global_time(hf2d_gpu* h, double global_time);
 int  hf2d_gpu_set_min_distance_to_wall(hf2d_gpu* h, const int* wall_ij, int n_wall, double x0,
                                        double* l_min, int* i_wall, int* j_wall, unsigned char* status);
 
+/* y+ of every set, non-solid node: replaces Recalc_y_plus(J, WallNodes) (deeps2d_core.cpp:2364-2386; start-up,
+ * hf2d_start.cpp:299; once per output cycle on rank 0 of the MPI build, :1723-1726).  i_wall, j_wall: the nearest wall node
+ * of each node (nx*ny ints each, x-major: the members SetMinDistanceToWall2D / hf2d_gpu_set_min_distance_to_wall left).
+ * The wall nodes' dUdy, dVdx are those of the last step (or of the records as uploaded, before any step).  The device
+ * y_plus plane the step reads is updated in place; y_plus (nx*ny doubles, may be NULL) receives the plane -- entries of
+ * unset / solid nodes are the plane as uploaded.  HF2D_EINVAL if some node's (i_wall, j_wall) is not a wall node (a deck
+ * without walls: the reference then reads node (0,0)'s gradients, which are not kept); y+ of those nodes is unchanged. */
+int  hf2d_gpu_recalc_y_plus(hf2d_gpu* h, const int* i_wall, const int* j_wall, double* y_plus);
+
 #ifdef __cplusplus
 }
 #endif

@@ -65,7 +65,7 @@ EXPORTS = ["hf2d_gpu_last_error", "hf2d_gpu_device_count", "hf2d_gpu_create", "h
            "hf2d_gpu_step_prepass", "hf2d_gpu_step_stage1", "hf2d_gpu_step_stage2", "hf2d_gpu_step_end", "hf2d_gpu_dt_ptr", "hf2d_gpu_stream",
            "hf2d_gpu_set_stream", "hf2d_gpu_set_timing", "hf2d_gpu_get_timing", "hf2d_gpu_dt_export", "hf2d_gpu_dt_import", "hf2d_gpu_launch_count",
            "hf2d_gpu_step_part", "hf2d_gpu_lane_fork", "hf2d_gpu_lane_join", "hf2d_gpu_side_stream", "hf2d_gpu_halo_pack_lane",
-           "hf2d_gpu_halo_unpack_lane", "hf2d_gpu_edge_tile_counts", "hf2d_gpu_set_min_distance_to_wall", "hf2d_gpu_set_global_time"]
+           "hf2d_gpu_halo_unpack_lane", "hf2d_gpu_edge_tile_counts", "hf2d_gpu_set_min_distance_to_wall", "hf2d_gpu_set_global_time", "hf2d_gpu_recalc_y_plus"]
 
 
 def lib():
@@ -113,6 +113,7 @@ def lib():
         L.hf2d_gpu_get_timing.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int)]
         L.hf2d_gpu_launch_count.argtypes = [C.c_void_p]
         L.hf2d_gpu_set_global_time.argtypes = [C.c_void_p, C.c_double]
+        L.hf2d_gpu_recalc_y_plus.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.hf2d_gpu_set_min_distance_to_wall.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_double, C.c_void_p, C.c_void_p,
                                                         C.c_void_p, C.c_void_p]
         L.hf2d_gpu_launch_count.restype = C.c_ulonglong
@@ -304,6 +305,15 @@ class Solver:
     def set_global_time(self, global_time: float):
         """GlobalTime of the running cycle: download_aos then writes FlowNode2D::time of the swept nodes (deeps2d_core.cpp:867)."""
         _ck(lib().hf2d_gpu_set_global_time(self._h, float(global_time)))
+
+    def recalc_y_plus(self, i_wall, j_wall):
+        """Recalc_y_plus(J, WallNodes) on the uploaded grid (deeps2d_core.cpp:2364-2386): returns the y_plus plane (nx, ny);
+        the device plane the step reads is updated in place."""
+        i_wall = np.ascontiguousarray(i_wall, dtype=np.int32); j_wall = np.ascontiguousarray(j_wall, dtype=np.int32)
+        assert i_wall.shape == (self.nx, self.ny) and j_wall.shape == (self.nx, self.ny)
+        y = np.empty((self.nx, self.ny), dtype=np.float64)
+        _ck(lib().hf2d_gpu_recalc_y_plus(self._h, i_wall.ctypes.data, j_wall.ctypes.data, y.ctypes.data))
+        return y
 
     def set_min_distance_to_wall(self, walls, x0: float = 0.0):
         """SetMinDistanceToWall2D(J, WallNodes, x0) on the uploaded grid (deeps2d_core.cpp:4783-4832).  walls: (n, 2) int

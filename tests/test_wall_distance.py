@@ -204,3 +204,65 @@ def test_reference_program_with_gpu_wall_distance(case, exact, tmp_path, monkeyp
         else:
             scale = max(float(np.abs(b).max()), 1e-300)
             assert float(np.abs(a - b).max()) / scale <= 1e-10, f
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", restart_case_names() + ["ns_keps_std_n8"])
+def test_gpu_y_plus_matches_reference(name):
+    """hf2d_gpu_recalc_y_plus on the reference's own start-up image (before any step: the wall gradients are those of the
+    records) against the y_plus member the reference's Recalc_y_plus left there -- bit-exact; y+ up to ~300 on the
+    restarted runs, identically 0 on a fresh one."""
+    from openhyperflow2d_b200 import cabi
+    c = load_case(name)
+    ref = c["state0"]
+    J = np.array(ref, copy=True)
+    J["y_plus"] = -5.0
+    s = cabi.Solver(c["cfg"], LAYOUT)
+    s.upload_aos(J)
+    y = s.recalc_y_plus(J["i_wall"], J["j_wall"])
+    s.close()
+    ct = np.ascontiguousarray(ref["CT"], dtype=np.uint64)
+    done = ((ct & 0x080000000) != 0) & ((ct & 0x040000000) == 0)
+    assert (y[done] == ref["y_plus"][done]).all()
+    assert (y[~done] == -5.0).all()
+    if name.startswith("restart/"):
+        assert float(y.max()) > 100.0
+
+
+@pytest.mark.gpu
+def test_gpu_y_plus_after_steps_uses_the_last_wall_gradients():
+    """After some steps the refresh must see the wall gradients of the LAST step (what the MPI build's per-cycle
+    Recalc_y_plus reads, deeps2d_core.cpp:1723-1726): oracle stepped alongside, then both refresh y+."""
+    from openhyperflow2d_b200 import cabi
+    from test_gpu_parity import REL_TOL, rel_linf
+    c = load_case("ns_laminar_n8")
+    cfg = c["cfg"]
+    nodes = O.nodes_from_ref(c["state0"])
+    J = np.array(c["state0"], copy=True)
+    s = cabi.Solver(cfg, LAYOUT)
+    s.upload_aos(J)
+    rc, dt_min, rep, tp = O.run_cycle(nodes, cfg, cfg["last_iter"], 5, cfg["dt"], 0.0)
+    assert rc == 0
+    s.step(5)
+    y = s.recalc_y_plus(J["i_wall"], J["j_wall"])
+    s.close()
+    yo = np.array(c["state0"]["y_plus"], copy=True)
+    O.recalc_y_plus(nodes["CT"], cfg["dx"], cfg["dy"], J["i_wall"], J["j_wall"], nodes["dUdy"], nodes["dVdx"], nodes["mu"],
+                    nodes["S"][..., 0], yo)
+    assert float(yo.max()) > 1.0
+    assert (y == yo).all(), rel_linf(y, yo)          # laminar: no transcendental on the path
+
+
+@pytest.mark.gpu
+def test_gpu_y_plus_refuses_a_nearest_wall_that_is_no_wall():
+    """The gradients of an ordinary gas node are intermediates that are not kept: naming one as the nearest wall is an
+    error (HF2D_EINVAL), and y+ stays as it was."""
+    from openhyperflow2d_b200 import cabi
+    c = load_case("ns_laminar_n8")
+    J = np.array(c["state0"], copy=True)
+    s = cabi.Solver(c["cfg"], LAYOUT)
+    s.upload_aos(J)
+    iw = np.full(J["i_wall"].shape, 5, dtype=np.int32); jw = np.full(J["i_wall"].shape, 30, dtype=np.int32)   # (5,30): free stream
+    with pytest.raises(cabi.Hf2dError):
+        s.recalc_y_plus(iw, jw)
+    s.close()
