@@ -210,6 +210,14 @@ int  hf2d_gpu_set_global_time(hf2d_gpu* h, double global_time);
 int  hf2d_gpu_set_min_distance_to_wall(hf2d_gpu* h, const int* wall_ij, int n_wall, double x0,
                                        double* l_min, int* i_wall, int* j_wall, unsigned char* status);
 
+/* Raw residual accumulators of the last step that reduced them -- RMS(k,ii), sumDiv(k,ii), iRMS(k,ii) and the largest
+ * |dS/S| of ONE sub-domain (deeps2d_core.cpp:1122-1153), HF2D_NEQ entries each, any pointer may be NULL.  A multi-GPU
+ * driver all-reduces them over its X-slabs (SUM, SUM, SUM, MAX) and finishes the norms once (:1539-1574 with a single
+ * sub-domain), which is what hf2d_step_report::sum_RMS of the undivided grid holds.  Replaces the Var_pack gather of the
+ * reference's MPI build (:1402-1463). */
+int  hf2d_gpu_residual_sums(hf2d_gpu* h, double rms[HF2D_NEQ], double sum_div[HF2D_NEQ],
+                            unsigned long long count[HF2D_NEQ], double dd_max[HF2D_NEQ]);
+
 /* y+ of every set, non-solid node: replaces Recalc_y_plus(J, WallNodes) (deeps2d_core.cpp:2364-2386; start-up,
  * hf2d_start.cpp:299; once per output cycle on rank 0 of the MPI build, :1723-1726).  i_wall, j_wall: the nearest wall node
  * of each node (nx*ny ints each, x-major: the members SetMinDistanceToWall2D / hf2d_gpu_set_min_distance_to_wall left).

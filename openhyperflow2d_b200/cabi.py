@@ -65,7 +65,7 @@ EXPORTS = ["hf2d_gpu_last_error", "hf2d_gpu_device_count", "hf2d_gpu_create", "h
            "hf2d_gpu_step_prepass", "hf2d_gpu_step_stage1", "hf2d_gpu_step_stage2", "hf2d_gpu_step_end", "hf2d_gpu_dt_ptr", "hf2d_gpu_stream",
            "hf2d_gpu_set_stream", "hf2d_gpu_set_timing", "hf2d_gpu_get_timing", "hf2d_gpu_dt_export", "hf2d_gpu_dt_import", "hf2d_gpu_launch_count",
            "hf2d_gpu_step_part", "hf2d_gpu_lane_fork", "hf2d_gpu_lane_join", "hf2d_gpu_side_stream", "hf2d_gpu_halo_pack_lane",
-           "hf2d_gpu_halo_unpack_lane", "hf2d_gpu_edge_tile_counts", "hf2d_gpu_set_min_distance_to_wall", "hf2d_gpu_set_global_time", "hf2d_gpu_recalc_y_plus"]
+           "hf2d_gpu_halo_unpack_lane", "hf2d_gpu_edge_tile_counts", "hf2d_gpu_set_min_distance_to_wall", "hf2d_gpu_set_global_time", "hf2d_gpu_recalc_y_plus", "hf2d_gpu_residual_sums"]
 
 
 def lib():
@@ -113,6 +113,7 @@ def lib():
         L.hf2d_gpu_get_timing.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int)]
         L.hf2d_gpu_launch_count.argtypes = [C.c_void_p]
         L.hf2d_gpu_set_global_time.argtypes = [C.c_void_p, C.c_double]
+        L.hf2d_gpu_residual_sums.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.hf2d_gpu_recalc_y_plus.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.hf2d_gpu_set_min_distance_to_wall.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_double, C.c_void_p, C.c_void_p,
                                                         C.c_void_p, C.c_void_p]
@@ -305,6 +306,12 @@ class Solver:
     def set_global_time(self, global_time: float):
         """GlobalTime of the running cycle: download_aos then writes FlowNode2D::time of the swept nodes (deeps2d_core.cpp:867)."""
         _ck(lib().hf2d_gpu_set_global_time(self._h, float(global_time)))
+
+    def residual_sums(self):
+        """Raw residual accumulators of the last reducing step: (rms, sum_div, count, dd_max), NEQ entries each."""
+        rms = np.zeros(NEQ); sd = np.zeros(NEQ); cnt = np.zeros(NEQ, dtype=np.uint64); dd = np.zeros(NEQ)
+        _ck(lib().hf2d_gpu_residual_sums(self._h, rms.ctypes.data, sd.ctypes.data, cnt.ctypes.data, dd.ctypes.data))
+        return rms, sd, cnt, dd
 
     def recalc_y_plus(self, i_wall, j_wall):
         """Recalc_y_plus(J, WallNodes) on the uploaded grid (deeps2d_core.cpp:2364-2386): returns the y_plus plane (nx, ny);

@@ -28,6 +28,39 @@ import numpy as np
 from . import cabi, gridgen
 
 
+def finish_residual_norms(rms, sum_div, count, cfg):
+    """Residual norms of one domain from its raw accumulators (deeps2d_core.cpp:1539-1574 with a single sub-domain; the
+    host side of hf2d_gpu_step's report, csrc/hf2d_step.inc fill_report): (sum_RMS[NEQ], max_RMS, k_max_RMS)."""
+    neq = len(rms)
+    out = np.zeros(neq)
+    for k in range(neq):
+        sr = 0.0
+        if cfg.get("isAlternateRMS", 0):
+            sd = 0.0
+            if sum_div[k] > 0.0:
+                sr += float(rms[k]); sd += float(sum_div[k])
+            sr = float(np.sqrt(sr / sd)) if (sd > 0.0 and sr > 0.0) else 0.0
+        else:
+            si = 0
+            if count[k] > 0:
+                sr += float(rms[k]); si += int(count[k])
+            sr = float(np.sqrt(sr / si)) if (si != 0 and sr > 0.0) else 0.0
+        out[k] = sr
+    mi = int(cfg.get("MonitorIndex", 0))
+    max_rms = 0.5 * float(cfg.get("ExitMonitorValue", 0.0)) if mi < 5 else 0.0       # :1488-1492
+    k_max = -1
+    if mi == 0 or mi > 4:
+        for k in range(neq):
+            max_rms = max(out[k], max_rms)
+            if max_rms == out[k]:
+                k_max = k
+    else:
+        max_rms = max(out[mi - 1], max_rms)
+        if max_rms == out[mi - 1]:
+            k_max = mi - 1
+    return out, max_rms, k_max
+
+
 class SlabProtocol:
     """The per-step exchange protocol, independent of what computes: `solver` offers the split-step / halo calls of
     cabi.Solver, buffers are torch tensors on `dev` (CUDA + NCCL in production, CPU + gloo in the protocol tests)."""
@@ -114,6 +147,23 @@ class SlabProtocol:
         s.dt_export(self.dtbuf.data_ptr())
         dist.all_reduce(self.dtbuf, op=dist.ReduceOp.MIN)
         s.dt_import(self.dtbuf.data_ptr())
+
+    def residuals(self, cfg):
+        """Residual norms of the WHOLE grid after a step that reduced them: every rank's raw accumulators
+        (hf2d_gpu_residual_sums) summed over the slabs -- one all-reduce of 3*NEQ doubles (SUM) and one of NEQ (MAX),
+        SURVEY 8e(3); replaces the reference's Var_pack gather (deeps2d_core.cpp:1402-1463) -- and the norm finished once,
+        as the undivided run does.  Returns (sum_RMS, max_RMS, k_max_RMS, DD_max); the same on every rank."""
+        torch = self.torch
+        rms, sd, cnt, dd = self.solver.residual_sums()
+        a = torch.tensor(np.concatenate([rms, sd, np.asarray(cnt, dtype=np.float64)]), dtype=torch.float64, device=self.dev)
+        m = torch.tensor(np.asarray(dd, dtype=np.float64), dtype=torch.float64, device=self.dev)
+        if self.world > 1:
+            dist = torch.distributed
+            dist.all_reduce(a, op=dist.ReduceOp.SUM)
+            dist.all_reduce(m, op=dist.ReduceOp.MAX)
+        a = a.cpu().numpy(); n = len(rms)
+        out, max_rms, k_max = finish_residual_norms(a[:n], a[n:2 * n], np.rint(a[2 * n:]).astype(np.int64), cfg)
+        return out, max_rms, k_max, m.cpu().numpy()
 
     # ---- stepping ----
     def step(self, n):

@@ -188,7 +188,7 @@ def test_plain_tiles_match_oracle(model, nsteps):
     np.testing.assert_allclose(list(rep.sum_RMS), list(orep.sum_RMS), rtol=1e-9, atol=1e-300)
 
 
-def _slab_run(model, nx, ny, nsteps, world):
+def _slab_run(model, nx, ny, nsteps, world, before_close=None):
     """`world` X-slabs on ONE GPU (one hf2d_gpu handle each, ghost columns, halo buffers handed over on the device):
     the same call sequence SlabRunner uses across GPUs, minus the transport."""
     import torch
@@ -257,6 +257,8 @@ def _slab_run(model, nx, ny, nsteps, world):
             s.step_end()
         torch.cuda.synchronize()
     out = np.array(Jfull, copy=True)
+    if before_close is not None:
+        before_close([s for s, *_ in slabs])
     for r, (s, J, gl, gr) in enumerate(slabs):
         s.download_aos(J)
         out[r * w:(r + 1) * w] = J[gl:J.shape[0] - gr]

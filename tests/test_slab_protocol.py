@@ -194,3 +194,71 @@ def test_lagged_chain_differs_only_through_the_chain(tmp_path):
     S = np.concatenate([np.load(tmp_path / f"r{r}.npy")[:-1] for r in range(world)]).reshape(nx, NY)
     assert not (S == ref.S).all()
     assert np.isfinite(S).all()
+
+
+# ---- residual norms of the whole grid from the slabs' raw accumulators ------------------------------------
+
+NEQ = 9
+
+
+def _fake_sums(S):
+    """Stand-in accumulators with the real ones' algebra: sums, a count and a maximum over the OWNED nodes, per 'equation'
+    (here: row k of the field; rows beyond NY stay empty as unused equations do)."""
+    rms = np.zeros(NEQ); sd = np.zeros(NEQ); cnt = np.zeros(NEQ, dtype=np.uint64); dd = np.zeros(NEQ)
+    for k in range(min(NEQ, S.shape[1])):
+        rms[k] = float((S[:, k] ** 2).sum()); sd[k] = float(np.abs(S[:, k]).sum()); cnt[k] = S.shape[0]; dd[k] = float(S[:, k].max())
+    return rms, sd, cnt, dd
+
+
+class FakeSolverWithSums(FakeSolver):
+    def residual_sums(self):
+        return _fake_sums(self.S[self.lo:self.hi])
+
+
+def _worker_residuals(rank, world, port, nx, nsteps, out_dir):
+    import torch
+    import torch.distributed as dist
+    from openhyperflow2d_b200.multigpu import SlabProtocol
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    w = nx // world
+    fs = FakeSolverWithSums(_field(nx), rank * w, w, rank, world)
+    p = SlabProtocol()
+    p._init_protocol(torch, fs, rank, world, torch.device("cpu"), "exact", "overlapped")
+    p.step(nsteps)
+    res = []
+    for alt, mi in ((1, 5), (0, 0), (1, 2)):
+        out, mx, km, dd = p.residuals({"isAlternateRMS": alt, "MonitorIndex": mi, "ExitMonitorValue": 1e-3})
+        res.append(np.concatenate([out, [mx, km], dd]))
+    np.save(os.path.join(out_dir, f"res{rank}.npy"), np.array(res))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_residual_norms_of_the_whole_grid(world, tmp_path):
+    """Every rank ends up with the norms the undivided run computes (sums over slabs, the square root taken once) --
+    not with the reference's several-sub-domain variant, which takes the root inside the sub-domain loop and thereby
+    depends on the decomposition (deeps2d_core.cpp:1541-1560)."""
+    import torch.multiprocessing as mp
+    from openhyperflow2d_b200.multigpu import finish_residual_norms
+    nx, nsteps = 12, 3
+    ref = FakeSolver(_field(nx), 0, nx, 0, 1)
+    for _ in range(nsteps):
+        ref.step_begin(); ref.step_stage1(); ref.step_stage2(); ref.step_end()
+    mp.spawn(_worker_residuals, args=(world, _free_port(), nx, nsteps, str(tmp_path)), nprocs=world, join=True)
+    got = [np.load(tmp_path / f"res{r}.npy") for r in range(world)]
+    for g in got[1:]:
+        assert (g == got[0]).all()                           # the same on every rank
+    rms, sd, cnt, dd = _fake_sums(ref.S)
+    for row, (alt, mi) in zip(got[0], ((1, 5), (0, 0), (1, 2))):
+        cfg = {"isAlternateRMS": alt, "MonitorIndex": mi, "ExitMonitorValue": 1e-3}
+        out, mx, km = finish_residual_norms(rms, sd, cnt, cfg)
+        np.testing.assert_allclose(row[:NEQ], out, rtol=1e-13, atol=0)
+        assert abs(row[NEQ] - mx) <= 1e-13 * mx and int(row[NEQ + 1]) == km
+        assert (row[NEQ + 2:] == dd).all()                  # a maximum is order independent
+        assert (out[NY:] == 0).all() and (out[:NY] > 0).all()
+    # the single-domain formulas themselves (csrc/hf2d_step.inc fill_report): alternate = sqrt(sum / sum_div), else sqrt(sum / n)
+    out, mx, km = finish_residual_norms(rms, sd, cnt, {"isAlternateRMS": 0, "MonitorIndex": 0})
+    assert out[0] == np.sqrt(rms[0] / int(cnt[0])) and km == int(np.argmax(out)) and mx == out.max()
+    out, mx, km = finish_residual_norms(rms, sd, cnt, {"isAlternateRMS": 1, "MonitorIndex": 3, "ExitMonitorValue": 0.0})
+    assert out[1] == np.sqrt(rms[1] / sd[1]) and km == 2 and mx == out[2]

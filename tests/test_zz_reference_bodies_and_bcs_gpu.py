@@ -160,3 +160,53 @@ def test_time_member_of_swept_nodes(name):
     assert float(ref.max()) > 0 and t_cycle_start > 0
     assert np.allclose(J["time"], ref, rtol=1e-12, atol=0.0)
     assert ((J["time"] != 0) == (ref != 0)).all()              # exactly the swept nodes
+
+
+@pytest.mark.parametrize("name", ["euler_duct_bff5_n7", "ns_keps_std_n8", "bc/euler_soft_n8"])
+def test_residual_sums_finish_to_the_report(name):
+    """hf2d_gpu_residual_sums (the raw accumulators a multi-GPU driver all-reduces) finished by the host formula of
+    multigpu.finish_residual_norms = the norms hf2d_gpu_step reports for the same step: same inputs, same arithmetic."""
+    from openhyperflow2d_b200 import cabi
+    from openhyperflow2d_b200.multigpu import finish_residual_norms
+    c = load_case(name)
+    J = np.array(c["state0"], copy=True)
+    s = cabi.Solver(c["cfg"], LAYOUT)
+    s.upload_aos(J)
+    rep = s.step(c["nsteps"])
+    rms, sd, cnt, dd = s.residual_sums()
+    s.close()
+    out, mx, km = finish_residual_norms(rms, sd, cnt, c["cfg"])
+    assert (out == np.array(list(rep.sum_RMS))).all()
+    assert (dd == np.array(list(rep.DD_max))).all()
+    assert mx == rep.max_RMS and km == rep.k_max_RMS
+    assert out.max() > 0
+
+
+@pytest.mark.parametrize("model", ["laminar", "keps"])
+def test_slab_residual_sums_add_up_to_the_single_domain(model):
+    """Two and four X-slabs on one GPU: their raw accumulators summed (what SlabProtocol.residuals all-reduces) and
+    finished once give the norms of the undivided run (summation order differs: 1e-9 relative)."""
+    from openhyperflow2d_b200 import gridgen
+    from openhyperflow2d_b200.multigpu import finish_residual_norms
+    from test_gpu_parity import _slab_run
+    nx, ny, nsteps = 96, 160, 4
+    _, cfg, _ = gridgen.three_cylinders(nx, ny, model=model)
+    res = {}
+    for world in (1, 2, 4):
+        got = {}
+
+        def grab(solvers):
+            parts = [q.residual_sums() for q in solvers]
+            got["rms"] = sum(p[0] for p in parts); got["sd"] = sum(p[1] for p in parts)
+            got["cnt"] = sum(p[2].astype(np.int64) for p in parts); got["dd"] = np.max([p[3] for p in parts], axis=0)
+
+        _slab_run(model, nx, ny, nsteps, world, before_close=grab)
+        res[world] = (finish_residual_norms(got["rms"], got["sd"], got["cnt"], cfg), got)
+    (want, _, km), g1 = res[1]
+    assert want.max() > 0
+    for world in (2, 4):
+        (out, _, k), g = res[world]
+        np.testing.assert_allclose(out, want, rtol=1e-9, atol=1e-300)
+        assert (g["cnt"] == g1["cnt"]).all()            # every swept node counted once: ghost columns do not contribute
+        assert (g["dd"] == g1["dd"]).all()
+        assert k == km
