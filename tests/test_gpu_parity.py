@@ -60,6 +60,12 @@ def check_against_reference(name, exact):
             same = (a == b) | ((a != a) & (b != b))
             assert same.all(), f"{name}: {f} differs in {int((~same).sum())} entries, rel-Linf {rel_linf(a, b):.3e}"
         else:
+            # where the reference itself produces NaN (the Chien model right after a restart: tests/golden/restart) the
+            # CUDA path must produce NaN in the same entries; the tolerance applies to the rest
+            na, nb = np.isnan(a), np.isnan(b)
+            assert (na == nb).all(), f"{name}: {f} NaN pattern differs in {int((na != nb).sum())} entries"
+            if nb.any():
+                a, b = np.where(nb, 0.0, a), np.where(nb, 0.0, b)
             if f in ("S", "A", "B", "beta", "SrcAdd", "F"):   # per-equation scaling
                 for k in range(a.shape[-1]):
                     assert rel_linf(a[..., k], b[..., k]) <= REL_TOL, f"{name}: {f}[{k}] rel-Linf {rel_linf(a[..., k], b[..., k]):.3e}"
