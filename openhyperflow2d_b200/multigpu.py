@@ -28,6 +28,29 @@ import numpy as np
 from . import cabi, gridgen
 
 
+def slab_cuts(ct, world, min_cols=2):
+    """X-slab boundaries with (nearly) equal numbers of ACTIVE nodes per slab: [(i0, i1), ...], slab r owns columns
+    [i0, i1).  The reference's rule (ScanArea, deeps2d_core.cpp:2153, 2207-2216) closes a sub-domain as soon as its
+    running count of set, non-solid nodes reaches total / n -- and leaves the columns after the last full quota to no
+    sub-domain at all when the division has a remainder; here every column is owned, the cut after slab r sits at the
+    first column where the prefix count reaches (r+1) * total / world, and no slab is narrower than `min_cols`.
+    ct: (nx, ny) flag words (CT, low 32 bits suffice)."""
+    ct = np.asarray(ct).astype(np.uint64)
+    nx = ct.shape[0]
+    assert world >= 1 and nx >= world * min_cols
+    active = ((ct & 0x80000000) != 0) & ((ct & 0x40000000) == 0)          # CT_NODE_IS_SET_2D and not CT_SOLID_2D
+    pre = np.concatenate([[0], np.cumsum(active.sum(axis=1))])           # pre[i] = active nodes in columns [0, i)
+    total = int(pre[-1])
+    cuts = [0]
+    for r in range(1, world):
+        i = int(np.searchsorted(pre, r * total / world, side="left"))
+        i = max(i, cuts[-1] + min_cols)
+        i = min(i, nx - (world - r) * min_cols)
+        cuts.append(i)
+    cuts.append(nx)
+    return [(cuts[r], cuts[r + 1]) for r in range(world)]
+
+
 def finish_residual_norms(rms, sum_div, count, cfg):
     """Residual norms of one domain from its raw accumulators (deeps2d_core.cpp:1539-1574 with a single sub-domain; the
     host side of hf2d_gpu_step's report, csrc/hf2d_step.inc fill_report): (sum_RMS[NEQ], max_RMS, k_max_RMS)."""

@@ -262,3 +262,30 @@ def test_residual_norms_of_the_whole_grid(world, tmp_path):
     assert out[0] == np.sqrt(rms[0] / int(cnt[0])) and km == int(np.argmax(out)) and mx == out.max()
     out, mx, km = finish_residual_norms(rms, sd, cnt, {"isAlternateRMS": 1, "MonitorIndex": 3, "ExitMonitorValue": 0.0})
     assert out[1] == np.sqrt(rms[1] / sd[1]) and km == 2 and mx == out[2]
+
+
+# ---- slab cuts by active nodes (SURVEY 8 f-2 / 8e "Partitioning") --------------------------------------------------------
+
+def test_slab_cuts_balance_active_nodes():
+    from golden_util import load_case
+    from openhyperflow2d_b200.multigpu import slab_cuts
+    for name in ("geometry/cylinders_keps_n8", "geometry/airfoil_keps_n8", "ns_keps_std_n8"):
+        ct = np.ascontiguousarray(load_case(name)["state0"]["CT"], dtype=np.uint64)
+        active = ((ct & 0x80000000) != 0) & ((ct & 0x40000000) == 0)
+        per_col = active.sum(axis=1)
+        for world in (1, 2, 3, 4, 8):
+            cuts = slab_cuts(ct, world)
+            assert cuts[0][0] == 0 and cuts[-1][1] == ct.shape[0]
+            assert all(a[1] == b[0] for a, b in zip(cuts, cuts[1:]))           # every column owned exactly once
+            assert all(i1 - i0 >= 2 for i0, i1 in cuts)
+            loads = [int(per_col[i0:i1].sum()) for i0, i1 in cuts]
+            assert sum(loads) == int(active.sum())
+            assert max(loads) - min(loads) <= 2 * int(per_col.max())            # within a column or two of each other
+    # a grid whose left half is solid: equal-column cuts would leave rank 0 idle, these do not
+    ct = np.full((40, 10), 0x80000000, dtype=np.uint64)
+    ct[:20] |= 0x40000000
+    cuts = slab_cuts(ct, 2)
+    assert cuts == [(0, 30), (30, 40)]
+    # degenerate: nothing active -> minimum widths still respected
+    cuts = slab_cuts(np.zeros((8, 4), dtype=np.uint64), 4)
+    assert all(i1 - i0 >= 2 for i0, i1 in cuts) and cuts[-1][1] == 8
