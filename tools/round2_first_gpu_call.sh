@@ -12,4 +12,5 @@ python -m pytest tests/test_zz_reference_bodies_and_bcs_gpu.py -m gpu -q    > gp
 python -m pytest tests -m gpu -q -x                                         > gpurun_out/r2_all_gpu_tests.log 2>&1
 # 3. bench line (the plain-tile kernels are byte-for-byte what round 1 measured: expect ~2.8 ms/step)
 python bench.py --steps 30 --warmup 5                                       > gpurun_out/r2_bench.log 2>&1
+python tools/bench_wall_distance.py                                         > gpurun_out/r2_wall_distance_bench.log 2>&1
 tail -3 gpurun_out/r2_wall_distance.log gpurun_out/r2_new_golden.log gpurun_out/r2_all_gpu_tests.log gpurun_out/r2_bench.log
