@@ -209,6 +209,12 @@ int  hf2d_gpu_set_global_time(hf2d_gpu* h, double global_time);
  *   i_wall, j_wall  the nearest wall node of status-1 nodes, -1 where the reference assigns none (member unchanged). */
 int  hf2d_gpu_set_min_distance_to_wall(hf2d_gpu* h, const int* wall_ij, int n_wall, double x0,
                                        double* l_min, int* i_wall, int* j_wall, unsigned char* status);
+/* The same for one X-slab of a larger grid (one handle per GPU): wall_ij and the returned i_wall hold GLOBAL columns,
+ * i_off = global column of the slab's column 0 (its left ghost column where it has one), nx_total = columns of the whole
+ * grid.  x is formed from the global index, so every slab computes bit for bit what the undivided call computes for its
+ * nodes (the reference's MPI build passes x0 = offset * dx instead, hf2d_start.cpp:171, whose rounding differs). */
+int  hf2d_gpu_set_min_distance_to_wall_slab(hf2d_gpu* h, const int* wall_ij, int n_wall, int i_off, int nx_total,
+                                            double* l_min, int* i_wall, int* j_wall, unsigned char* status);
 
 /* Raw residual accumulators of the last step that reduced them -- RMS(k,ii), sumDiv(k,ii), iRMS(k,ii) and the largest
  * |dS/S| of ONE sub-domain (deeps2d_core.cpp:1122-1153), HF2D_NEQ entries each, any pointer may be NULL.  A multi-GPU

@@ -65,7 +65,7 @@ EXPORTS = ["hf2d_gpu_last_error", "hf2d_gpu_device_count", "hf2d_gpu_create", "h
            "hf2d_gpu_step_prepass", "hf2d_gpu_step_stage1", "hf2d_gpu_step_stage2", "hf2d_gpu_step_end", "hf2d_gpu_dt_ptr", "hf2d_gpu_stream",
            "hf2d_gpu_set_stream", "hf2d_gpu_set_timing", "hf2d_gpu_get_timing", "hf2d_gpu_dt_export", "hf2d_gpu_dt_import", "hf2d_gpu_launch_count",
            "hf2d_gpu_step_part", "hf2d_gpu_lane_fork", "hf2d_gpu_lane_join", "hf2d_gpu_side_stream", "hf2d_gpu_halo_pack_lane",
-           "hf2d_gpu_halo_unpack_lane", "hf2d_gpu_edge_tile_counts", "hf2d_gpu_set_min_distance_to_wall", "hf2d_gpu_set_global_time", "hf2d_gpu_recalc_y_plus", "hf2d_gpu_residual_sums"]
+           "hf2d_gpu_halo_unpack_lane", "hf2d_gpu_edge_tile_counts", "hf2d_gpu_set_min_distance_to_wall", "hf2d_gpu_set_global_time", "hf2d_gpu_recalc_y_plus", "hf2d_gpu_residual_sums", "hf2d_gpu_set_min_distance_to_wall_slab"]
 
 
 def lib():
@@ -113,6 +113,8 @@ def lib():
         L.hf2d_gpu_get_timing.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int)]
         L.hf2d_gpu_launch_count.argtypes = [C.c_void_p]
         L.hf2d_gpu_set_global_time.argtypes = [C.c_void_p, C.c_double]
+        L.hf2d_gpu_set_min_distance_to_wall_slab.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                                             C.c_void_p, C.c_void_p, C.c_void_p]
         L.hf2d_gpu_residual_sums.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.hf2d_gpu_recalc_y_plus.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.hf2d_gpu_set_min_distance_to_wall.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_double, C.c_void_p, C.c_void_p,
@@ -321,6 +323,17 @@ class Solver:
         y = np.empty((self.nx, self.ny), dtype=np.float64)
         _ck(lib().hf2d_gpu_recalc_y_plus(self._h, i_wall.ctypes.data, j_wall.ctypes.data, y.ctypes.data))
         return y
+
+    def set_min_distance_to_wall_slab(self, walls, i_off: int, nx_total: int):
+        """The slab form: `walls` and the returned i_wall are GLOBAL columns, i_off = global column of local column 0."""
+        walls = np.ascontiguousarray(walls, dtype=np.int32).reshape(-1, 2)
+        nx, ny = self.nx, self.ny
+        l_min = np.empty((nx, ny), dtype=np.float64)
+        i_wall = np.empty((nx, ny), dtype=np.int32); j_wall = np.empty((nx, ny), dtype=np.int32)
+        status = np.empty((nx, ny), dtype=np.uint8)
+        _ck(lib().hf2d_gpu_set_min_distance_to_wall_slab(self._h, walls.ctypes.data, len(walls), int(i_off), int(nx_total),
+                                                         l_min.ctypes.data, i_wall.ctypes.data, j_wall.ctypes.data, status.ctypes.data))
+        return l_min, i_wall, j_wall, status
 
     def set_min_distance_to_wall(self, walls, x0: float = 0.0):
         """SetMinDistanceToWall2D(J, WallNodes, x0) on the uploaded grid (deeps2d_core.cpp:4783-4832).  walls: (n, 2) int

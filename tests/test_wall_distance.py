@@ -266,3 +266,33 @@ def test_gpu_y_plus_refuses_a_nearest_wall_that_is_no_wall():
     with pytest.raises(cabi.Hf2dError):
         s.recalc_y_plus(iw, jw)
     s.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["geometry/cylinders_keps_n8", "ns_keps_std_n8"])
+def test_gpu_wall_distance_in_slabs_equals_the_undivided_grid(name):
+    """Two and three X-slabs (ghost columns included, one handle each): the slab form takes the GLOBAL wall list and forms x
+    from the global column index, so every slab reproduces the reference's undivided result for its nodes bit for bit."""
+    from openhyperflow2d_b200 import cabi
+    c = load_case(name)
+    ref = c["state0"]
+    nx = ref.shape[0]
+    ct = np.ascontiguousarray(ref["CT"], dtype=np.uint64)
+    walls = O.wall_nodes(ct)
+    set_gas = ((ct & 0x080000000) != 0) & ((ct & 0x040000000) == 0)
+    for world in (2, 3):
+        w = nx // world
+        for r in range(world):
+            gl, gr = (1 if r > 0 else 0), (1 if r < world - 1 else 0)
+            i0, i1 = r * w - gl, (nx if r == world - 1 else (r + 1) * w) + gr
+            J = np.array(ref[i0:i1], copy=True)
+            J["l_min"] = 77.0
+            cfg = dict(c["cfg"]); cfg["MaxX"] = J.shape[0]
+            s = cabi.Solver(cfg, LAYOUT, rank=r, n_ranks=world)
+            s.upload_aos(J)
+            l_min, i_wall, j_wall, status = s.set_min_distance_to_wall_slab(walls, i0, nx)
+            s.close()
+            done = status == 1
+            assert (done == set_gas[i0:i1]).all()
+            assert (l_min[done] == ref["l_min"][i0:i1][done]).all(), (world, r)
+            assert (i_wall[done] == ref["i_wall"][i0:i1][done]).all() and (j_wall[done] == ref["j_wall"][i0:i1][done]).all()
