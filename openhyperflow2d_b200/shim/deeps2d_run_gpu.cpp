@@ -136,9 +136,29 @@ void DEEPS2D_Run(ofstream* f_stream) {
             if (ws[n] == 1) { nd.l_min = wl[n]; if (wi[n] >= 0) { nd.i_wall = wi[n]; nd.j_wall = wj[n]; } }
             else if (ws[n] == 2) { nd.SetCond2D(CT_SOLID_2D); n_solid++; }        // deeps2d_core.cpp:4797
         }
-        delete[] wl; delete[] wi; delete[] wj; delete[] ws;
         if (n_solid && hf2d_gpu_upload_aos(h, J->GetMatrixPtr(), &lay, pinned)) die(f_stream, "upload");
         *f_stream << "hf2d_gpu: wall distance of " << WallNodes->GetNumElements() << " wall nodes on the GPU\n" << flush;
+        // y+ from the same start-up data on the device (Recalc_y_plus, hf2d_start.cpp:299), with i_wall / j_wall as J now
+        // holds them.  main() has computed it on the host already: the two are compared, the device plane is what the
+        // steps read.  (A deck without walls names node (0,0) as everybody's wall: refused, the host values stand.)
+        for (int i = 0; i < MaxX; i++) for (int j = 0; j < MaxY; j++) {
+            const size_t n = (size_t)i * MaxY + j;
+            wi[n] = J->GetValue(i, j).i_wall; wj[n] = J->GetValue(i, j).j_wall;
+        }
+        if (hf2d_gpu_recalc_y_plus(h, wi, wj, wl) == 0) {
+            long n_diff = 0;
+            for (int i = 0; i < MaxX; i++) for (int j = 0; j < MaxY; j++) {
+                Node& nd = J->GetValue(i, j);
+                if (!nd.isCond2D(CT_NODE_IS_SET_2D) || nd.isCond2D(CT_SOLID_2D)) continue;
+                const double y = wl[(size_t)i * MaxY + j];
+                if (!(y == nd.y_plus)) n_diff++;
+                nd.y_plus = y;
+            }
+            *f_stream << "hf2d_gpu: y+ on the GPU: " << n_diff << " nodes differ from the host's\n" << flush;
+        } else {
+            *f_stream << "hf2d_gpu: y+ left to the host (" << hf2d_gpu_last_error() << ")\n" << flush;
+        }
+        delete[] wl; delete[] wi; delete[] wj; delete[] ws;
     }
     *f_stream << "hf2d_gpu: DEEPS2D time loop on the GPU (" << MaxX << "x" << MaxY << " nodes)\n" << flush;
 

@@ -193,8 +193,9 @@ def test_reference_program_with_gpu_wall_distance(case, exact, tmp_path, monkeyp
     monkeypatch.setenv("HF2D_GPU_WALL_DISTANCE", "1")
     Jg, rms_g, out = D._run(D.GPU, deck, case, str(tmp_path / "gpu"))
     assert "wall nodes on the GPU" in out
+    assert "y+ on the GPU: 0 nodes differ from the host's" in out       # hf2d_gpu_recalc_y_plus on the same start-up data
     assert len(rms_g) == len(rms_r)
-    for f in ("l_min", "i_wall", "j_wall", "CT"):
+    for f in ("l_min", "i_wall", "j_wall", "CT", "y_plus"):
         assert (Jg[f] == Jr[f]).all(), f
     assert (Jr["l_min"] > 0).any()
     for f in ("S", "Tg", "mu_t"):

@@ -91,8 +91,9 @@ def test_wall_gradients_come_back_for_a_restart(name):
         assert (J[f][off] == c["state0"][f][off]).all()      # everything else: as uploaded
 
 
-@pytest.mark.parametrize("case,exact", [("ns_laminar", True), ("ns_prandtl_vd", False)])
-def test_restart_chain_through_the_reference_program(case, exact, tmp_path):
+@pytest.mark.parametrize("case,exact,gpu_startup", [("ns_laminar", True, False), ("ns_prandtl_vd", False, False),
+                                                    ("ns_laminar", True, True), ("ns_prandtl_vd", False, True)])
+def test_restart_chain_through_the_reference_program(case, exact, gpu_startup, tmp_path, monkeypatch):
     """Swap-file checkpoint / restart, end to end: the reference program with its time loop on the GPU
     (oracle/_ref/ohf_gpu) runs 8 steps, leaves its swap file, is started AGAIN from it and runs 6 more; the unmodified
     program does the same.  The second start-up recomputes y_plus from the wall gradients of the first run's image
@@ -124,7 +125,11 @@ def test_restart_chain_through_the_reference_program(case, exact, tmp_path):
         return np.fromfile(os.path.join(wd, case + ".hf2d"), dtype=aos.ref_dtype(LAYOUT)).reshape(nx, ny), outs
 
     Jr, _ = chain(D.REF, str(tmp_path / "ref"))
+    if gpu_startup:     # wall distance and y+ of BOTH start-ups on the GPU as well (HF2D_GPU_WALL_DISTANCE)
+        monkeypatch.setenv("HF2D_GPU_WALL_DISTANCE", "1")
     Jg, outs = chain(D.GPU, str(tmp_path / "gpu"))
+    if gpu_startup:     # second start-up: non-zero y+ from the first run's wall gradients, device == host on the same records
+        assert all("y+ on the GPU: 0 nodes differ from the host's" in o for o in outs)
     assert "hf2d_gpu: DEEPS2D time loop on the GPU" in outs[0] and "hf2d_gpu: DEEPS2D time loop on the GPU" in outs[1]
     assert float(np.abs(Jr["y_plus"]).max()) > 1.0
     for f in ("y_plus", "l_min", "S", "Tg", "mu_t", "U", "V"):
