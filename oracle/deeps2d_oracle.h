@@ -96,14 +96,14 @@ int ohf_run_cycle(ohf_node* J, const ohf_cfg* cfg, unsigned last_iter, int nstep
 }
 #endif
 /* Wall nodes and wall distance (GetWallNodes, deeps2d_core.cpp:2081-2104; SetMinDistanceToWall2D, :4783-4832):
- * planar, x-major.  Pinned by tests/test_wall_distance.py against l_min / i_wall / j_wall of the reference's own
+ * planar, x-major.  Pinned by tests/test_zzz_wall_distance.py against l_min / i_wall / j_wall of the reference's own
  * pre-step images (tests/golden: the reference runs both at start-up of every Navier-Stokes case). */
 long ohf_get_wall_nodes(const uint64_t* ct, int nx, int ny, int* out_ij);
 void ohf_set_min_distance_to_wall(uint64_t* ct, const double* Tg, const double* p, int nx, int ny, double dx, double dy,
                                   double x0, const int* wall_ij, long n_wall, double* l_min, int* i_wall, int* j_wall,
                                   unsigned char* status);
 
-/* Recalc_y_plus (deeps2d_core.cpp:2364-2386), planar; pinned by tests/test_wall_distance.py against the y_plus member of
+/* Recalc_y_plus (deeps2d_core.cpp:2364-2386), planar; pinned by tests/test_zzz_wall_distance.py against the y_plus member of
  * the reference's start-up images of RESTARTED runs (tests/golden/restart: the only ones with non-zero wall gradients). */
 void ohf_recalc_y_plus(const uint64_t* ct, int nx, int ny, double dx, double dy, const int* i_wall, const int* j_wall,
                        const double* dUdy, const double* dVdx, const double* mu, const double* rho, double* y_plus);

@@ -6,7 +6,7 @@
 mkdir -p gpurun_out
 set -x
 # 1. unrun code paths: wall distance + y+ kernels, wall-gradient write-back, time stamp, new golden groups
-python -m pytest tests/test_wall_distance.py -m gpu -q                      > gpurun_out/r2_wall_distance.log 2>&1
+python -m pytest tests/test_zzz_wall_distance.py -m gpu -q                      > gpurun_out/r2_wall_distance.log 2>&1
 python -m pytest tests/test_zz_reference_bodies_and_bcs_gpu.py -m gpu -q    > gpurun_out/r2_new_golden.log 2>&1
 # 2. the established suite (must still be green: Stage 2 general tiles and k_pack changed)
 python -m pytest tests -m gpu -q -x                                         > gpurun_out/r2_all_gpu_tests.log 2>&1
