@@ -21,6 +21,8 @@ struct Local {
     double Yfu, Yox, Ycp, Yair;   // mass fractions inside chemistry at the point where R/CP/lam/mu are formed
     double Y[4];            // FlowNode2D::Y after chemistry
     double Upre, Vpre;      // S[RhoU]/S[Rho], S[RhoV]/S[Rho] of a no-slip wall node before the wall reset (virtual sources)
+    double Ut, Vt;          // U, V as TurbModRANS2D sees them: after the U_CONST/V_CONST block, BEFORE the wall-law /
+                            // no-slip rewrites (hyper_flow_node.hpp:413-435 run before :447-488)
     bool   filled;          // FillNode2D ran past its early returns
     bool   active, fc;
 };
@@ -91,6 +93,7 @@ __device__ __forceinline__ void local_rest(D& dv, const LD& ld, const Params& P,
     L.s7c = L.S[7]; L.s8c = L.S[8];
     L.Uo = ld.U(); L.Vo = ld.V(); L.Tgo = ld.Tg();
     L.U = L.Uo; L.V = L.Vo; L.Tg = L.Tgo;
+    L.Ut = L.Uo; L.Vt = L.Vo;
     L.CP = ld.CP(); L.R = ld.R();
     L.mu = KC::ns ? ld.mu() : 0.;
     const double kg_old = ld.kg();
@@ -103,6 +106,7 @@ __device__ __forceinline__ void local_rest(D& dv, const LD& ld, const Params& P,
         L.kg = dv.div(L.CP, L.CP - L.R);
         if (is_set(ct, CT_U_CONST)) L.S[iRhoU] = L.U * L.S[iRho]; else L.U = dv.div(L.S[iRhoU], L.S[iRho]);
         if (is_set(ct, CT_V_CONST)) L.S[iRhoV] = L.V * L.S[iRho]; else L.V = dv.div(L.S[iRhoV], L.S[iRho]);
+        L.Ut = L.U; L.Vt = L.V;
         if (KC::ns && (tt & TT_MASK) != 0) {
             // the S-rewriting part of TurbModRANS2D (:753-779 k-eps, :856-862 SA)
             if (is_set(tt, TCT_Prandtl_Model)) {

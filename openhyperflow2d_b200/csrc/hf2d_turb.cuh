@@ -41,7 +41,7 @@ __device__ __forceinline__ void turb_own(D& dv, const LD& ld, const Params& P, c
         const double Tmp1 = g.dUdy + g.dVdx;
         const double Tmp2 = rho * l;
         double Tmp3 = g.dUdx * g.dUdx + g.dVdy * g.dVdy;
-        if (KC::axi) Tmp3 += dv.div(L.U, yj);
+        if (KC::axi) Tmp3 += dv.div(L.Ut, yj);
         if (T.mu_t == 0) T.mu_t = rho * l * l * OMAX(fabs(g.dUdy), fabs(g.dVdx));
         G = T.mu_t * (Tmp1 * Tmp1 + 2 * Tmp3);
         // Rt and the damping functions see S[k], S[eps] as committed, before this call's boundary rewrites
@@ -72,7 +72,7 @@ __device__ __forceinline__ void turb_own(D& dv, const LD& ld, const Params& P, c
         if (is_init) { if (S8 != 0) T.mu_t = fabs(dv.div(C_mu * f_mu * S7 * S7, S8)); }
         if (is_mu_t && S8 != 0) { const double nu_t = fabs(dv.div(C_mu * f_mu * S7 * S7, S8)); T.mu_t = OMIN(nu_t, T.mu_t); }
         if (!is_init) {
-            T.A7 = S7 * L.U; T.A8 = S8 * L.U; T.B7 = S7 * L.V; T.B8 = S8 * L.V;
+            T.A7 = S7 * L.Ut; T.A8 = S8 * L.Ut; T.B7 = S7 * L.Vt; T.B8 = S8 * L.Vt;
             const double mk = dv.div(T.mu_t, sig_k), me = dv.div(T.mu_t, sig_eps);
             const double RX7 = (L.mu + mk) * g.dkdx, RX8 = (L.mu + me) * g.depsdx;
             const double RY7 = (L.mu + mk) * g.dkdy, RY8 = (L.mu + me) * g.depsdy;
@@ -113,7 +113,7 @@ __device__ __forceinline__ void turb_own(D& dv, const LD& ld, const Params& P, c
             const double gg = r + Cw2 * (pow(r, 6.0) - r);
             const double fw = gg * pow((1.0 + pow(Cw3, 6.0)) / (pow(gg, 6.0) + pow(Cw3, 6.0)), 1.0 / 6.0);
             const double ft2 = Ct2 * exp(-Ct4 * ksi * ksi);
-            T.A7 = S7 * L.U; T.B7 = S7 * L.V;
+            T.A7 = S7 * L.Ut; T.B7 = S7 * L.Vt;
             const double Div_nu = (g.dkdx + g.dkdy);
             const double RX7 = dv.div((nu + S7) * g.dkdx, sig), RY7 = dv.div((nu + S7) * g.dkdy, sig);
             T.A7 = T.A7 - RX7; T.B7 = T.B7 - RY7; T.wAB7 = true;

@@ -115,7 +115,7 @@ void DEEPS2D_Run(ofstream* f_stream) {
     // already run the host version by the time DEEPS2D_Run is called (hf2d_start.cpp:298) -- a maintainer would drop that
     // call -- so its results are wiped from J first: what the step and the swap file see is what the GPU computed.
     const bool gpu_wall_distance = getenv("HF2D_GPU_WALL_DISTANCE") && atoi(getenv("HF2D_GPU_WALL_DISTANCE")) &&
-                                   ProblemType == SM_NS && WallNodes;
+                                   ProblemType == SM_NS && WallNodes && WallNodes->GetNumElements() > 0;   // (no walls: the host's i_wall = j_wall = 0 stand)
     if (gpu_wall_distance) {
         for (int i = 0; i < MaxX; i++) for (int j = 0; j < MaxY; j++) {
             Node& nd = J->GetValue(i, j);
@@ -136,6 +136,7 @@ void DEEPS2D_Run(ofstream* f_stream) {
             if (ws[n] == 1) { nd.l_min = wl[n]; if (wi[n] >= 0) { nd.i_wall = wi[n]; nd.j_wall = wj[n]; } }
             else if (ws[n] == 2) { nd.SetCond2D(CT_SOLID_2D); n_solid++; }        // deeps2d_core.cpp:4797
         }
+        // (nodes the kernel re-typed as solid change the boundary lists: the image is uploaded again before y+)
         if (n_solid && hf2d_gpu_upload_aos(h, J->GetMatrixPtr(), &lay, pinned)) die(f_stream, "upload");
         *f_stream << "hf2d_gpu: wall distance of " << WallNodes->GetNumElements() << " wall nodes on the GPU\n" << flush;
         // y+ from the same start-up data on the device (Recalc_y_plus, hf2d_start.cpp:299), with i_wall / j_wall as J now
@@ -159,6 +160,10 @@ void DEEPS2D_Run(ofstream* f_stream) {
             *f_stream << "hf2d_gpu: y+ left to the host (" << hf2d_gpu_last_error() << ")\n" << flush;
         }
         delete[] wl; delete[] wi; delete[] wj; delete[] ws;
+        // One download contract for both image paths: every byte the step does not own comes back AS UPLOADED.  l_min,
+        // y_plus, i_wall, j_wall were just written into J on the host, so J goes up once more -- the resident device
+        // image (and the planes the steps read) then hold exactly what J holds now.
+        if (hf2d_gpu_upload_aos(h, J->GetMatrixPtr(), &lay, pinned)) die(f_stream, "upload");
     }
     *f_stream << "hf2d_gpu: DEEPS2D time loop on the GPU (" << MaxX << "x" << MaxY << " nodes)\n" << flush;
 
