@@ -142,7 +142,7 @@ int  hf2d_gpu_bytes_per_cell(hf2d_gpu* h, double* bytes);
 
 /* Multi-GPU (X-slabs, one process per GPU): pack the columns the neighbours need into `buf` / consume received
  * ones.  side: 0 = left neighbour, 1 = right neighbour.  phase: 0 = full edge columns after Stage 2 (both ways),
- * 1 = shadow S of the edge column between Stage 1 and Stage 2 (left -> right), 2 = S of the edge column after the
+ * 1 = NEW state (S, U, V, Tg) of the edge column between K1 and K2 (left -> right), 2 = S of the edge column after the
  * Neumann pre-pass (left -> right; makes Neumann chains that cross a seam exact) -- see DESIGN.md "seams".  `buf` is device memory of hf2d_gpu_halo_bytes() bytes. */
 size_t hf2d_gpu_halo_bytes(hf2d_gpu* h, int phase);
 int  hf2d_gpu_halo_pack(hf2d_gpu* h, int side, int phase, void* dev_buf);
@@ -195,6 +195,14 @@ unsigned long long hf2d_gpu_launch_count(hf2d_gpu* h);      /* kernels launched 
  * Optional: once set, hf2d_gpu_download_aos writes it into the `time` member of the swept nodes; never set, that member
  * comes back as uploaded.  Call it before the download of each cycle with the cycle's GlobalTime (before += CurrentTimePart). */
 int  hf2d_gpu_set_global_time(hf2d_gpu* h, double global_time);
+
+/* Gradient members of the records (droYdx[4], droYdy[4], dUdx .. dTdy, dkdx .. depsdy; deeps2d_core.cpp:1169-1238).  They are
+ * intermediates of a step -- never stored in HBM -- but a run RESTARTED from the swap file re-runs FillNode2D(0,1) on every
+ * node with the values its records hold (InitDEEPS2D, deeps2d_core.cpp:4565; ScanArea with isTurbulenceReset, :2186-2205).
+ * enable != 0 (the default): the LAST step of every hf2d_gpu_step / hf2d_gpu_step_continue call also writes them to 18
+ * planes (allocated on first use) and hf2d_gpu_download_aos puts them into the records, exactly the members the reference
+ * assigns on each node.  A shim that steps in chunks switches this off and on again before the last chunk of a cycle. */
+int  hf2d_gpu_keep_gradients(hf2d_gpu* h, int enable);
 
 /* Wall distance of every set, non-solid node of the uploaded grid: replaces SetMinDistanceToWall2D(J, WallNodes, x0)
  * (deeps2d_core.cpp:4783-4832; called at start-up of every Navier-Stokes run, hf2d_start.cpp:127, :171, :298 -- an

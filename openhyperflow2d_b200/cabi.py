@@ -65,7 +65,7 @@ EXPORTS = ["hf2d_gpu_last_error", "hf2d_gpu_device_count", "hf2d_gpu_create", "h
            "hf2d_gpu_step_prepass", "hf2d_gpu_step_stage1", "hf2d_gpu_step_stage2", "hf2d_gpu_step_end", "hf2d_gpu_dt_ptr", "hf2d_gpu_stream",
            "hf2d_gpu_set_stream", "hf2d_gpu_set_timing", "hf2d_gpu_get_timing", "hf2d_gpu_dt_export", "hf2d_gpu_dt_import", "hf2d_gpu_launch_count",
            "hf2d_gpu_step_part", "hf2d_gpu_lane_fork", "hf2d_gpu_lane_join", "hf2d_gpu_side_stream", "hf2d_gpu_halo_pack_lane",
-           "hf2d_gpu_halo_unpack_lane", "hf2d_gpu_edge_tile_counts", "hf2d_gpu_set_min_distance_to_wall", "hf2d_gpu_set_global_time", "hf2d_gpu_recalc_y_plus", "hf2d_gpu_residual_sums", "hf2d_gpu_set_min_distance_to_wall_slab"]
+           "hf2d_gpu_halo_unpack_lane", "hf2d_gpu_edge_tile_counts", "hf2d_gpu_set_min_distance_to_wall", "hf2d_gpu_set_global_time", "hf2d_gpu_recalc_y_plus", "hf2d_gpu_residual_sums", "hf2d_gpu_set_min_distance_to_wall_slab", "hf2d_gpu_keep_gradients"]
 
 
 def lib():
@@ -120,6 +120,7 @@ def lib():
         L.hf2d_gpu_set_min_distance_to_wall.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_double, C.c_void_p, C.c_void_p,
                                                         C.c_void_p, C.c_void_p]
         L.hf2d_gpu_launch_count.restype = C.c_ulonglong
+        L.hf2d_gpu_keep_gradients.argtypes = [C.c_void_p, C.c_int]
         _lib = L
     return _lib
 
@@ -300,7 +301,7 @@ class Solver:
     def get_timing(self):
         ms, cnt = (C.c_double * 2)(), (C.c_int * 2)()
         _ck(lib().hf2d_gpu_get_timing(self._h, ms, cnt))
-        return {"stage1_plain_ms": ms[0], "stage2_plain_ms": ms[1], "launches": (cnt[0], cnt[1])}
+        return {"k1_plain_ms": ms[0], "k2_plain_ms": ms[1], "launches": (cnt[0], cnt[1])}
 
     def launch_count(self) -> int:
         return int(lib().hf2d_gpu_launch_count(self._h))
@@ -308,6 +309,10 @@ class Solver:
     def set_global_time(self, global_time: float):
         """GlobalTime of the running cycle: download_aos then writes FlowNode2D::time of the swept nodes (deeps2d_core.cpp:867)."""
         _ck(lib().hf2d_gpu_set_global_time(self._h, float(global_time)))
+
+    def keep_gradients(self, enable=True):
+        """The last step of every step call keeps the 18 gradient members for the download (restart fidelity); default on."""
+        _ck(lib().hf2d_gpu_keep_gradients(self._h, int(enable)))
 
     def residual_sums(self):
         """Raw residual accumulators of the last reducing step: (rms, sum_div, count, dd_max), NEQ entries each."""

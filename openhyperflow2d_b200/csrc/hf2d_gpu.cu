@@ -4,7 +4,8 @@
 #include "../../include/hf2d_gpu.h"
 #include "hf2d_dev.cuh"
 #include "hf2d_stage1.cuh"
-#include "hf2d_stage2.cuh"
+#include "hf2d_point.cuh"
+#include "hf2d_flux.cuh"
 #include "hf2d_heat.cuh"
 
 #include <algorithm>
@@ -59,10 +60,9 @@ struct hf2d_gpu {
     void* d_stage; size_t stage_bytes;
     void* d_image; size_t image_bytes;   // the raw record image, resident when it fits (hf2d_io.inc)
     double bytes_per_cell;
-    // strip-sweep tiles (hf2d_stage2.cuh): TI columns x S2_WARPS strips of STRIP_ROWS rows
+    // tiles (hf2d_point.cuh): TI columns x TILE_H rows, one warp each
     int TI, n_sb, n_tx;
     int *d_tiles_plain, *d_tiles_gen; int n_plain, n_gen;
-    int* d_tiles_s1; int n_s1;      // Stage-1 list of the plain tiles, adjacent tiles merged (hf2d_io.inc)
     int n_plain_edge, n_gen_edge;   // the first n_*_edge tiles of each list touch a ghost column (X-slab seams): hf2d_gpu_step_part
     bool s2_pending;                // Stage-2 parts queued, planes not yet swapped (hf2d_gpu_step_part S2_FINISH does)
     int plain_ttc;                  // TurbType word of the plain tiles (-1: no plain kernel for this grid)
@@ -71,6 +71,8 @@ struct hf2d_gpu {
     bool prepass_done;              // hf2d_gpu_step_prepass already ran for the current step
     double global_time; bool have_global_time;   // GlobalTime of the running cycle (hf2d_gpu_set_global_time): FlowNode2D::time at download
     int rms_every;                  // residual norms are reduced on steps with iter % rms_every == 0 and on the last step of a call
+    bool keep_grads;                // hf2d_gpu_keep_gradients: the last step of every step call writes the 18 gradient planes
+    bool grads_this_step, grads_valid;
 };
 
 extern "C" const char* hf2d_gpu_last_error(void) { return g_err; }
@@ -139,7 +141,7 @@ extern "C" int hf2d_gpu_create(const hf2d_cfg* cfg, int device, hf2d_gpu** out) 
     P.tab = h->d_tab; P.st = h->d_st;
     h->last_iter_cycle = cfg->last_iter;
     h->rms_every = cfg->NOutStep; h->prepass_done = false; h->timing = false; h->tn[0] = h->tn[1] = 0;
-    h->TI = 16; h->n_sb = h->n_tx = 0; h->d_tiles_plain = h->d_tiles_gen = nullptr; h->n_plain = h->n_gen = 0; h->n_plain_edge = h->n_gen_edge = 0; h->d_tiles_s1 = nullptr; h->n_s1 = 0; h->s2_pending = false; h->n_chains_local = 0; h->d_nlist_seam = nullptr; h->n_nlist_seam = 0; h->prepass_local_done = false; h->ahead = false; h->plain_ttc = -1;
+    h->TI = 16; h->n_sb = h->n_tx = 0; h->d_tiles_plain = h->d_tiles_gen = nullptr; h->n_plain = h->n_gen = 0; h->n_plain_edge = h->n_gen_edge = 0; h->s2_pending = false; h->n_chains_local = 0; h->d_nlist_seam = nullptr; h->n_nlist_seam = 0; h->prepass_local_done = false; h->ahead = false; h->plain_ttc = -1; h->keep_grads = true; h->grads_this_step = false; h->grads_valid = false;
     *out = h;
     return HF2D_OK;
 }
@@ -160,6 +162,17 @@ extern "C" int hf2d_gpu_destroy(hf2d_gpu* h) {
 }
 
 static bool plain_ttc_supported(int ttc);
+// the 18 gradient planes exist only for callers that asked for them (hf2d_gpu_keep_gradients)
+static int ensure_grad_planes(hf2d_gpu* h) {
+    if (h->P.grad || !h->P.ns) return 0;
+    if (dalloc(h, &h->P.grad, (size_t)G_COUNT * h->P.N)) return HF2D_ECUDA;
+    return 0;
+}
+extern "C" int hf2d_gpu_keep_gradients(hf2d_gpu* h, int enable) {
+    if (!h) return fail(HF2D_EINVAL, "null");
+    h->keep_grads = enable != 0;
+    return HF2D_OK;
+}
 #include "hf2d_io.inc"
 #include "hf2d_step.inc"
 #include "hf2d_walldist.inc"

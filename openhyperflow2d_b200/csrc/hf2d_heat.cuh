@@ -18,7 +18,7 @@ __device__ __forceinline__ bool heat_visitor(const Params& P, int vi, int vj, lo
 }
 
 // running Q_conv of solid node (si,sj) after the visits up to and including visitor number `upto` (0..3)
-__device__ __forceinline__ double heat_chain(const Params& P, const double* __restrict__ Tg, int si, int sj, int upto) {
+__device__ __forceinline__ double heat_chain(const Params& P, const double* __restrict__ Tg, const double* __restrict__ lam, int si, int sj, int upto) {
     const long long s = (long long)si * P.ny + sj;
     const double Ts = Tg[s];
     const int vi[4] = {si - 1, si, si, si + 1}, vj[4] = {sj, sj - 1, sj + 1, sj};
@@ -27,7 +27,7 @@ __device__ __forceinline__ double heat_chain(const Params& P, const double* __re
         long long v;
         if (!heat_visitor(P, vi[q], vj[q], v)) continue;
         const double d = (q == 0 || q == 3) ? P.dx : P.dy;
-        double lam_eff = P.lam[v] + P.spec[P.spec_idx[v]].lam_t;
+        double lam_eff = lam[v] + P.spec[P.spec_idx[v]].lam_t;
         lam_eff = lam_eff / 1;
         if (Q > 0.) Q = (Q - lam_eff * (Ts - Tg[v]) / d) * 0.5;
         else Q = -lam_eff * (Ts - Tg[v]) / d;
@@ -35,8 +35,8 @@ __device__ __forceinline__ double heat_chain(const Params& P, const double* __re
     return Q;
 }
 
-// Tg: the planes Stage 2 just wrote (the heat source runs after the sweep, deeps2d_core.cpp:1402)
-__global__ void k_wall_heat(Params P, const double* __restrict__ Tg, const int* __restrict__ wall_list, int n_wall) {
+// Tg, lam: the planes K1 just wrote (the heat source runs after the sweep, deeps2d_core.cpp:1402)
+__global__ void k_wall_heat(Params P, const double* __restrict__ Tg, const double* __restrict__ lam, const int* __restrict__ wall_list, int n_wall) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n_wall) return;
     SpecNode& sp = P.spec[wall_list[t]];
@@ -52,7 +52,7 @@ __global__ void k_wall_heat(Params P, const double* __restrict__ Tg, const int* 
         if (si[d] < 0 || si[d] >= P.nx || sj[d] < 0 || sj[d] >= P.ny) continue;
         const long long s = (long long)si[d] * P.ny + sj[d];
         if (!is_set(P.ct[s], CT_SOLID)) continue;
-        const double Q = heat_chain(P, Tg, si[d], sj[d], slot[d]);
+        const double Q = heat_chain(P, Tg, lam, si[d], sj[d], slot[d]);
         sp.Q_conv[d] = Q;
         sp.SrcAdd[iRhoE] = -dt * Q / ((d < 2) ? P.dy : P.dx);
     }

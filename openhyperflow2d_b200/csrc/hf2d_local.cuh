@@ -43,10 +43,7 @@ template <int NS, int AXI, int TTC> struct KCfg {
     static constexpr bool plain = TTC >= 0;
 };
 
-// Where a node's own Stage-2 inputs come from.  General tiles read the planes directly; plain tiles read the warp's
-// staged copy of the column in shared memory (hf2d_stage2.cuh), filled by cp.async one column ahead of the sweep.
-enum { PL_S = 0, PL_SN = NEQ, PL_U = 2 * NEQ, PL_V, PL_TG, PL_CP, PL_R, PL_KG, PL_P, PL_MU, PL_MUT, PL_LAM, PL_LMIN, PL_COUNT };
-#define TILE_ROWS 33   // 31 owned rows + the halo row below + the row above (up neighbour of the last owner)
+// Where a node's own inputs come from: last step's planes.
 struct GlobalLoad {
     const Params& P; long long m;
     __device__ __forceinline__ double S(int k) const { return P.S_in[(long long)k * P.N + m]; }
@@ -57,30 +54,12 @@ struct GlobalLoad {
     __device__ __forceinline__ double CP() const { return P.CP_in[m]; }
     __device__ __forceinline__ double R() const { return P.R_in[m]; }
     __device__ __forceinline__ double kg() const { return P.kg_in[m]; }
-    __device__ __forceinline__ double p() const { return P.p[m]; }
+    __device__ __forceinline__ double p() const { return P.p_in[m]; }
     __device__ __forceinline__ double mu() const { return P.mu_in[m]; }
     __device__ __forceinline__ double mu_t() const { return P.mu_t[m]; }
-    __device__ __forceinline__ double lam() const { return P.lam[m]; }
+    __device__ __forceinline__ double lam() const { return P.lam_in[m]; }
     __device__ __forceinline__ double lmin() const { return P.l_min[m]; }
 };
-struct TileLoad {
-    const double* t;   // this lane's element of plane 0 of the staged column; planes are TILE_ROWS doubles apart
-    __device__ __forceinline__ double pl(int q) const { return t[q * TILE_ROWS]; }
-    __device__ __forceinline__ double S(int k) const { return pl(PL_S + k); }
-    __device__ __forceinline__ double SN(int k) const { return pl(PL_SN + k); }
-    __device__ __forceinline__ double U() const { return pl(PL_U); }
-    __device__ __forceinline__ double V() const { return pl(PL_V); }
-    __device__ __forceinline__ double Tg() const { return pl(PL_TG); }
-    __device__ __forceinline__ double CP() const { return pl(PL_CP); }
-    __device__ __forceinline__ double R() const { return pl(PL_R); }
-    __device__ __forceinline__ double kg() const { return pl(PL_KG); }
-    __device__ __forceinline__ double p() const { return pl(PL_P); }
-    __device__ __forceinline__ double mu() const { return pl(PL_MU); }
-    __device__ __forceinline__ double mu_t() const { return pl(PL_MUT); }
-    __device__ __forceinline__ double lam() const { return pl(PL_LAM); }
-    __device__ __forceinline__ double lmin() const { return pl(PL_LMIN); }
-};
-
 // The part of local_update that follows the commit loop: L.S[] holds the committed S of node m.
 // FULL=false computes only what neighbours read (S[0], S[4..8] post-chemistry, U, V, Tg).
 template <class KC, bool FULL, class D, class LD>

@@ -1,4 +1,6 @@
-// hf2d_stage1.cuh -- Stage 1 of the DEEPS2D step (deeps2d_core.cpp:853-1026) as parallel kernels.
+// hf2d_stage1.cuh -- the ordered part of Stage 1 of the DEEPS2D step (deeps2d_core.cpp:853-1026): the Neumann
+// in-place overwrite as a parallel pre-pass, and the per-step scalar kernels.  Stage 1 proper lives in k_point
+// (hf2d_point.cuh).
 //
 // The reference sweeps i-outer/j-inner IN PLACE: a node with a d/dx=0 or d/dy=0 flag overwrites its own S[k]
 // from its neighbours before the update, and nodes visited later see the overwritten value while nodes visited
@@ -7,7 +9,7 @@
 //   k_neumann_level  : level by level (level = longest chain of Neumann nodes through left/down neighbours)
 //                      apply the overwrite in place, reading left/down from the array (already new) and
 //                      right/up through S0 when that neighbour is itself a list node (still old)
-//   k_stage1         : every node: own/left/down S from the array (new), right/up S through S0 if listed (old)
+//   k_point (Stage 1): every node: own/left/down S from the array (new), right/up S through S0 if listed (old)
 #pragma once
 #include "hf2d_dev.cuh"
 
@@ -23,7 +25,7 @@ __global__ void k_begin_step(Params P) {
     s->CFL_scn = tab_get(dv, &P.tab[12], it);
     if ((int)s->iter < P.TurbStartIter) { s->is_mu_t = 0; s->is_init = P.isTurbulenceReset; }
     else { s->is_mu_t = 1; s->is_init = 0; }
-    for (int k = 0; k < NEQ; k++) { s->RMS[k] = 0.; s->sumDiv[k] = 0.; s->iRMS[k] = 0ull; s->DDmax_bits[k] = 0ull; }
+    for (int k = 0; k < NEQ; k++) { s->RMS[k] = 0.; s->sumDiv[k] = 0.; s->iRMS[k] = 0ull; s->DDmax_bits[k] = 0ull; s->nan_last[k] = 0ull; s->DDfix_bits[k] = 0ull; }
     s->block_counter = 0;
 }
 
@@ -184,96 +186,5 @@ __device__ __forceinline__ double ds_new(const Params& P, long long m, int k, in
         const double m_m_1 = 1. / (double)OMAX(n3 + n4, 1);
         const double* Bk = P.B + (long long)k * P.N;
         return (Bk[m + n3] - Bk[m - n4]) * m_m_1;
-    }
-}
-
-// Strip sweep (same tiles as Stage 2, hf2d_stage2.cuh): a warp owns STRIP_ROWS consecutive rows and walks TI columns.
-// KC::plain instantiations serve tiles whose nodes and whole neighbour ring are unflagged interior nodes: every
-// equation is advanced with plain central differences, no special-node look-ups.
-#define STRIP_ROWS 31
-#define S1_WARPS 4
-#ifndef S1_MERGE
-#define S1_MERGE 1            // plain tiles merged per Stage-1 walk (<= 8: 3 bits of the list entry).  2 makes k_stage1<plain> itself
-                              // faster (0.76 -> 0.71 ms) but the step slower (2.91 -> 2.99 ms): its longer-lived blocks keep the general
-                              // tiles of the side stream waiting for SM slots, and Stage 2 waits for those (profiles/NOTES.md)
-#endif
-#define S1_THREADS (32 * S1_WARPS)
-
-template <class KC>
-__global__ void __launch_bounds__(S1_THREADS) k_stage1(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int t_idx = blockIdx.x * S1_WARPS + warp;
-    if (t_idx >= n_tiles) return;
-    const int entry = tiles[t_idx];
-    const int tile = entry & 0x0fffffff, merged = (entry >> 28) + 1;     // Stage-1 plain list: up to S1_MERGE adjacent tiles per walk
-    const int tx = tile / n_sb, sb = tile - tx * n_sb;
-    const int j = sb * STRIP_ROWS + lane;
-    if (lane >= STRIP_ROWS || j >= P.ny) return;
-    const int i0 = P.i_lo + tx * TI, i1 = min(i0 + TI * merged, P.i_hi);
-    const long long ny = P.ny, N = P.N;
-    const double dt = P.st->dt;
-    const double dtdx = ddiv(dt, P.dx), dtdy = ddiv(dt, P.dy);                  // :843-844
-    const double dyy = ddiv(P.dx, P.dx + P.dy), dxx = ddiv(P.dy, P.dx + P.dy);   // :643-644
-    for (int i = i0; i < i1; i++) {
-        const long long n = (long long)i * ny + j;
-        uint32_t ct, tt;
-        if (KC::plain) { ct = CT_NODE_IS_SET; tt = (uint32_t)KC::ttc | TT_IDXL | TT_IDXR | TT_IDYU | TT_IDYD; }
-        else { ct = P.ct[n]; tt = P.tt[n]; }
-        const bool act = node_active(ct);
-        const int ne = act ? num_eq(tt) : 0;
-        // tracked dS planes must be carried over for nodes / equations that are not advanced
-        if (!KC::plain && (P.need_dsx | P.need_dsy)) {
-            for (int k = 0; k < NEQ; k++) {
-                const bool adv = act && k < ne && (eq_flags(ct, tt, k, KC::ns) & 1);
-                if (!adv) {
-                    if (P.need_dsx & (1u << k)) P.dSx_out[k][n] = P.dSx_in[k][n];
-                    if (P.need_dsy & (1u << k)) P.dSy_out[k][n] = P.dSy_in[k][n];
-                }
-            }
-        }
-        if (!act) continue;
-        const int n1 = (tt & TT_IDXL) ? 1 : 0, n2 = (tt & TT_IDXR) ? 1 : 0, n3 = (tt & TT_IDYU) ? 1 : 0, n4 = (tt & TT_IDYD) ? 1 : 0;
-        const long long nL = n - n1 * ny, nR = n + n2 * ny, nU = n + n3, nD = n - n4;
-        const double n_n_1 = (n1 + n2 == 2) ? 0.5 : 1., m_m_1 = (n3 + n4 == 2) ? 0.5 : 1.;   // 1/max(n1+n2,1), 1/max(n3+n4,1)
-        uint32_t ttR = 0u, ttU = 0u;
-        if (!KC::plain) { ttR = n2 ? P.tt[nR] : 0u; ttU = n3 ? P.tt[nU] : 0u; }
-        const SpecNode* sp = (tt & TT_SPEC) ? &P.spec[P.spec_idx[n]] : nullptr;
-#pragma unroll
-        for (int k = 0; k < NEQ; k++) {
-            if (k >= ne) continue;
-            const unsigned f = eq_flags(ct, tt, k, KC::ns);
-            if (!(f & 1)) continue;
-            const long long o = (long long)k * N;
-            const double beta = P.beta[o + n], _beta = 1. - beta;
-            const double sc = P.S_in[o + n];
-            const double sl = P.S_in[o + nL], sd = P.S_in[o + nD];
-            const double sr = n2 ? s_old(P, nR, ttR, k) : sc;
-            const double su = n3 ? s_old(P, nU, ttU, k) : sc;
-            double dXX, dYY;
-            if (f & 2) dXX = (P.A[o + nR] - P.A[o + nL]) * n_n_1; else dXX = 0.;
-            if (f & 4) dYY = (P.B[o + nU] - P.B[o + nD]) * m_m_1; else dYY = 0.;
-            if (P.need_dsx & (1u << k)) P.dSx_out[k][n] = dXX;
-            if (P.need_dsy & (1u << k)) P.dSy_out[k][n] = dYY;
-            if (f & 8) {    // :1008-1010  left: this sweep's value, right: last step's (own value if aliased)
-                const double dl = n1 ? ds_new<KC>(P, nL, k, 0) : dXX;
-                const double dr = n2 ? P.dSx_in[k][nR] : dXX;
-                dXX = (dl + dr) * 0.5;
-            }
-            if (f & 16) {   // :1011-1013
-                const double du = n3 ? P.dSy_in[k][nU] : dYY;
-                const double dd = n4 ? ds_new<KC>(P, nD, k, 1) : dYY;
-                dYY = (du + dd) * 0.5;
-            }
-            double src = 0.;
-            if (k >= 7 || P.has_src) src = P.Src[o + n];
-            const double srcadd = sp ? sp->SrcAdd[k] : 0.;
-            double sn;
-            if (KC::axi) {
-                sn = sc * beta + _beta * (dxx * (sl + sr) + dyy * (su + sd)) * 0.5 - (dtdx * dXX + dtdy * (dYY + ddiv(P.F[o + n], (double)(j + 1)))) + src * dt + srcadd;
-            } else {
-                sn = sc * beta + _beta * (dxx * (sl + sr) + dyy * (su + sd)) * 0.5 - (dtdx * dXX + dtdy * dYY) + src * dt + srcadd;
-            }
-            P.SN[o + n] = sn;
-        }
     }
 }

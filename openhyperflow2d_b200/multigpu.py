@@ -211,7 +211,7 @@ class SlabProtocol:
         P = type(s)
         s.step_begin()
         self._handoff_prepass(0)
-        s.step_part(P.S1_GENERAL, 0); s.step_part(P.S1_PLAIN, 0); s.step_part(P.S1_FINISH, 0)
+        s.step_part(P.S1_GENERAL, 0, want_rms); s.step_part(P.S1_PLAIN, 0, want_rms); s.step_part(P.S1_FINISH, 0, want_rms)
         self._mid_exchange()
         s.step_part(P.S2_EDGE, 0, want_rms); s.step_part(P.S2_INNER, 0, want_rms)
         self._end_exchange()
@@ -228,10 +228,10 @@ class SlabProtocol:
         with self._lane(1):
             if not getattr(self, "_prepass_ahead", False):
                 self._handoff_prepass(1)
-            s.step_part(P.S1_GENERAL, 1)
-        s.step_part(P.S1_PLAIN, 0)
+            s.step_part(P.S1_GENERAL, 1, want_rms)
+        s.step_part(P.S1_PLAIN, 0, want_rms)
         s.lane_join()
-        s.step_part(P.S1_FINISH, 0)
+        s.step_part(P.S1_FINISH, 0, want_rms)
         s.lane_fork()
         s.step_part(P.S2_INNER, 0, want_rms)     # the bulk is queued first: nothing below waits for it
         with self._lane(1):

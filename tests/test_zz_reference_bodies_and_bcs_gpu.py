@@ -42,6 +42,22 @@ def test_gpu_matches_reference_on_bc_branches(name):
     check_against_reference(name, exact=not any(t in name for t in ("keps", "ns_sa")))     # pow() / exp() closures
 
 
+def assert_rms_close(got, want, cfg, S_before, S_after):
+    """Residual norms of one step, GPU vs oracle.  With isAlternateRMS = 1 the reference's serial build sums SIGNED
+    differences, RMS[k] = sqrt(sum(S_next - S) / sum(S^2)) (deeps2d_core.cpp:1138-1143): the numerator cancels, so a sum in
+    another order (atomics vs the sweep) is only accurate relative to sum|S_next - S|, not to its own value -- and when it
+    comes out <= 0 the norm is reported as 0.  The tolerance is therefore set on the numerator: 1e-14 * sum|dS| (~100 ulp; double
+    rounding over <= 1e5 terms stays far below that), on top of 1e-9 relative."""
+    got, want = np.asarray(list(got)), np.asarray(list(want))
+    if not cfg["isAlternateRMS"]:
+        np.testing.assert_allclose(got, want, rtol=1e-9, atol=1e-300)
+        return
+    for k in range(len(want)):
+        den = float((S_before[..., k] ** 2).sum())
+        slack = 1e-14 * float(np.abs(S_after[..., k] - S_before[..., k]).sum()) / den if den > 0 else 0.0
+        assert abs(got[k] ** 2 - want[k] ** 2) <= 1e-9 * want[k] ** 2 + slack, (k, got[k], want[k], slack)
+
+
 @pytest.mark.parametrize("name", ["geometry/cylinders_keps_n8", "geometry/airfoil_keps_n8", "bc/euler_soft_n8", "bc/ns_keps_soft_mud2k_n8",
                                   "restart/ns_keps_chien_r12_n6", "restart/ns_prandtl_vd_r12_n6"])
 def test_gpu_matches_oracle_stepwise_on_rasterised_bodies(name):
@@ -56,23 +72,29 @@ def test_gpu_matches_oracle_stepwise_on_rasterised_bodies(name):
     s.upload_aos(J)
     dt_min = cfg["dt"]
     for it in range(c["nsteps"]):
+        S_before = np.array(nodes["S"], dtype=float, copy=True)
         rc, dt_min, orep = O.step(nodes, cfg, cfg["last_iter"] + it, 0, dt_min)
         assert rc == 0
         grep = s.step(1)
         assert grep.dt == orep.dt
         assert abs(grep.dt_min - orep.dt_min) <= 1e-13 * orep.dt_min
-        np.testing.assert_allclose(list(grep.sum_RMS), list(orep.sum_RMS), rtol=1e-9, atol=1e-300)
+        assert_rms_close(grep.sum_RMS, orep.sum_RMS, cfg, S_before, np.asarray(nodes["S"], float))
         np.testing.assert_allclose(list(grep.DD_max), list(orep.DD_max), rtol=1e-9, atol=1e-300)
     s.close()
 
 
+GRAD_MEMBERS = ["droYdx", "droYdy", "dUdx", "dUdy", "dVdx", "dVdy", "dTdx", "dTdy", "dkdx", "dkdy", "depsdx", "depsdy"]
+
+
 @pytest.mark.parametrize("name", ["ns_laminar_n8", "ns_keps_std_n8", "ns_keps_std_n4x2", "geometry/cylinders_keps_n8",
-                                  "geometry/airfoil_keps_n8", "geometry/rect_laminar_n8", "restart/ns_keps_chien_r12_n6"])
-def test_wall_gradients_come_back_for_a_restart(name):
-    """dUdy, dVdx of the wall nodes are the two gradient members something reads after the step: the start-up of a run
-    restarted from the swap file derives y_plus from them (Recalc_y_plus, deeps2d_core.cpp:2364-2386).  Stage 2 keeps
-    them in the boundary table and hf2d_gpu_download_aos writes them into the records; every other gradient member is an
-    intermediate and comes back as uploaded."""
+                                  "geometry/airfoil_keps_n8", "geometry/rect_laminar_n8", "restart/ns_keps_chien_r12_n6",
+                                  "bc/ns_sa_subsonic_n4", "bc/ns_laminar_mixed_flags_n8", "bc/ns_keps_wall_law_n2"])
+def test_gradient_members_come_back_for_a_restart(name):
+    """The 18 gradient members of the records are intermediates of a step, but a run restarted from the swap file re-runs
+    FillNode2D(0,1) on every node with them (InitDEEPS2D, deeps2d_core.cpp:4565) and Recalc_y_plus reads the wall nodes'
+    dUdy, dVdx (:2364-2386).  The last step of a step call keeps them (hf2d_gpu_keep_gradients, default on) and
+    hf2d_gpu_download_aos writes exactly the members the reference assigns: the whole image must then agree with the
+    reference's in every gradient member, on every node."""
     from test_gpu_parity import REL_TOL, rel_linf, run_gpu
     c = load_case(name)
     J, _, _ = run_gpu(c)
@@ -81,14 +103,14 @@ def test_wall_gradients_come_back_for_a_restart(name):
     wall = ((ct & 0x040000000) == 0) & (((ct & 0x04000000) != 0) | ((ct & 0x08000000) != 0))
     assert wall.sum() > 0
     for f in ("dUdy", "dVdx"):
-        a, b = J[f][wall], ref[f][wall]
-        assert np.abs(b).max() > 0, (name, f)
+        assert np.abs(ref[f][wall]).max() > 0, (name, f)
+    for f in GRAD_MEMBERS:
+        a, b = np.asarray(J[f], float), np.asarray(ref[f], float)
         if "laminar" in name:
-            assert (a == b).all(), (name, f, int((a != b).sum()))
+            same = (a == b) | ((a != a) & (b != b))
+            assert same.all(), (name, f, int((~same).sum()))
         else:
             assert rel_linf(a, b) <= REL_TOL, (name, f, rel_linf(a, b))
-        off = ~wall
-        assert (J[f][off] == c["state0"][f][off]).all()      # everything else: as uploaded
 
 
 @pytest.mark.parametrize("case,exact,gpu_startup", [("ns_laminar", True, False), ("ns_prandtl_vd", False, False),

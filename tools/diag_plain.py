@@ -17,7 +17,7 @@ for f in ("S", "A", "B", "beta"):
         bad = (a[..., k] != b[..., k]) & ~((a[..., k] != a[..., k]) & (b[..., k] != b[..., k]))
         if bad.any():
             idx = np.argwhere(bad)
-            print(f, k, "bad", len(idx), "i range", idx[:, 0].min(), idx[:, 0].max(), "j%31 hist", np.bincount(idx[:, 1] % 31, minlength=31).tolist(),
+            print(f, k, "bad", len(idx), "i range", idx[:, 0].min(), idx[:, 0].max(), "j%31 hist", np.bincount(idx[:, 1] % 32, minlength=32).tolist(),
                   "i%16 hist", np.bincount(idx[:, 0] % 16, minlength=16).tolist(), "first", idx[:5].tolist(),
                   "worst", [(int(i), int(j), float(a[i, j, k]), float(b[i, j, k])) for i, j in
                             np.argwhere(np.abs(a[..., k] - b[..., k]) > 0.1 * np.abs(a[..., k] - b[..., k]).max())[:6]],
