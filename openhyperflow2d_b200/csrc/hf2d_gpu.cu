@@ -5,6 +5,7 @@
 #include "hf2d_dev.cuh"
 #include "hf2d_stage1.cuh"
 #include "hf2d_point.cuh"
+#include "hf2d_stage1_plain.cuh"
 #include "hf2d_flux.cuh"
 #include "hf2d_heat.cuh"
 

@@ -126,7 +126,11 @@ k_point(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI, 
                 }
             }
         }
-        if (act) {
+        if constexpr (KC::plain) {
+            // plain tiles: K1a (k_stage1_plain) has written NextNode->S and the new blending factors, equation by equation
+#pragma unroll
+            for (int k = 0; k < NE_C; k++) if (valid_j) sn[k] = P.SN[(long long)k * N + n];
+        } else if (act) {
             const int n1 = (tt & TT_IDXL) ? 1 : 0, n2 = (tt & TT_IDXR) ? 1 : 0, n3 = (tt & TT_IDYU) ? 1 : 0, n4 = (tt & TT_IDYD) ? 1 : 0;
             const long long nL = n - n1 * ny, nR = n + n2 * ny, nU = n + n3, nD = n - n4;
             const double n_n_1 = (n1 + n2 == 2) ? 0.5 : 1., m_m_1 = (n3 + n4 == 2) ? 0.5 : 1.;   // 1/max(n1+n2,1), 1/max(n3+n4,1)
@@ -177,52 +181,10 @@ k_point(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI, 
 #pragma unroll
         for (int k = 0; k < NEQ; k++) L.S[k] = 0.;
         if constexpr (KC::plain) {
-            // every equation k < NE_C is advanced and committed
-            double so[NEQ], bo[NEQ];
+            // every equation k < NE_C is advanced and committed (K1a did the residual and the blending factor);
+            // S[7], S[8] of a laminar / algebraic-model node stay what they are
 #pragma unroll
-            for (int k = 0; k < NEQ; k++) { so[k] = 0.; bo[k] = 0.; if (valid_j && (k < NE_C || k < 7 || TURB_C)) so[k] = P.S_in[(long long)k * N + n]; }
-            if (P.bFF & 1) {
-#pragma unroll
-                for (int k = 0; k < NE_C; k++) if (valid_j) bo[k] = P.beta[(long long)k * N + n];
-            }
-            auto phaseA = [&](auto& dv, auto rms) {
-                const double beta_min = OMIN(P.beta0, st.beta_scn);
-                const double bb = beta_min * beta_min;
-                // absent species (S[4..6] == 0 on every node of the warp's column: single-gas runs) take no residual and leave
-                // beta alone (res == false below): their 6 divisions + 3 square roots are skipped as ONE block
-                bool sp_any = false;
-#pragma unroll
-                for (int k = 4; k < 7; k++) sp_any |= upd && so[k] != 0.;
-                sp_any = __any_sync(0xffffffffu, sp_any);
-#pragma unroll
-                for (int k = 0; k < NE_C; k++) {
-                    if (k >= 4 && k < 7 && !sp_any) continue;
-                    const bool res = upd && so[k] != 0.;
-                    double sqrt_RES;
-                    const double DD = residual_dd(dv, so[k], sn[k], res, sqrt_RES, P.bFF);
-                    const double xx = (P.bFF >= 4) ? sqrt_RES : (P.bFF >= 2) ? DD * DD : DD;
-                    const double cap = (P.bFF & 1) ? (beta_min + bo[k]) * 0.5 : beta_min;
-                    const double quo = dv.div(bb, beta_min + xx, res);
-                    if (res) P.beta[(long long)k * N + n] = OMIN(cap, quo);
-                    if constexpr (decltype(rms)::value) {
-                        double c_rms = 0., c_div = 0.;
-                        const bool isnan_dd = res && DD != DD;
-                        if (res) { if (P.isAlternateRMS) { c_div = so[k] * so[k]; c_rms = sn[k] - so[k]; } else { c_rms = DD * DD; } }
-                        const double a = warp_sum(c_rms), b = warp_sum(c_div);
-                        const unsigned c = __reduce_add_sync(0xffffffffu, res ? 1u : 0u);
-                        const unsigned long long d = warp_max_u64((res && !isnan_dd) ? d2bits(DD) : 0ull);
-                        if (isnan_dd) atomicMax(&P.st->nan_last[k], (unsigned long long)n + 1ull);
-                        if (lane == 0 && c) {
-                            sh_acc[warp][k] += a; sh_acc[warp][NEQ + k] += b; sh_u[warp][k] += c;
-                            if (d > sh_u[warp][NEQ + k]) sh_u[warp][NEQ + k] = d;
-                        }
-                    }
-                }
-            };
-            if (want_rms) { DivExact e; phaseA(e, std::true_type()); }     // output steps only: exact policy, fused reduction
-            else run([&](auto& dv) { phaseA(dv, std::false_type()); });
-#pragma unroll
-            for (int k = 0; k < NEQ; k++) L.S[k] = !valid_j ? 0. : (k < NE_C) ? sn[k] : so[k];
+            for (int k = 0; k < NEQ; k++) L.S[k] = !valid_j ? 0. : (k < NE_C) ? sn[k] : (k < 7 || TURB_C) ? P.S_in[(long long)k * N + n] : 0.;
         } else {
             DivExact dv;
 #pragma unroll
