@@ -195,15 +195,20 @@ def reference_arm(args):
     print(json.dumps(line))
 
 
-def stage2_bytes_per_cell(model, axi=False):
-    """Algorithmic bytes per cell of ONE k_stage2 launch (kernels): every plane the kernel owns read once and
-    written once, neighbour reads served on chip.  reads S, SN [Neq each], U,V,Tg,CP,R,k,p [+ mu, mu_t, lam, l_min if NS];
-    writes beta, S, A, B [Neq each], U,V,Tg,R,CP,k,p [+ mu, lam, mu_t if NS] [+ Src(Neq-7)] [+ F(Neq) if axisymmetric]."""
+def kernel_bytes_per_cell(model, axi=False):
+    """Algorithmic bytes per plain cell of ONE launch of each of the three plain-tile kernels: every
+    plane a kernel owns read once / written once, neighbour reads served on chip.
+      K1a k_stage1_plain: reads S, beta, A, B [Neq each], Src [Neq-7], (F [Neq] axisymmetric), (dSdy[eps] k-eps); writes SN, beta [Neq each], (dSdy[eps])
+      K1b k_point:        reads SN [Neq], CP, R, k; writes S [Neq], U, V, Tg, k, p, R, CP (+ mu, lam NS)
+      K2  k_flux:         reads S_new [Neq], SN[4..6], U, V, Tg, p, k (new), S_old[0,4..Neq-1], U, V, Tg (old), CP, R, k (old)
+                          (+ mu, lam, mu_t, l_min NS); writes A, B [Neq each], (F), Src [Neq-7], mu_t"""
     neq = {"keps": 9, "sa": 8}.get(model, 7)
     ns = model != "euler"
-    r = 2 * neq + 7 + (4 if ns else 0)
-    w = 4 * neq + 7 + (3 if ns else 0) + (neq - 7) + (neq if axi else 0)
-    return 8.0 * (r + w)
+    ke = 1 if model == "keps" else 0
+    k1a = (4 * neq + (neq - 7) + (neq if axi else 0) + ke) + (2 * neq + ke)
+    k1b = (neq + 3) + (neq + 7 + (2 if ns else 0))
+    k2 = (neq + 3 + 5 + (neq - 3) + 3 + 3 + (4 if ns else 0)) + (2 * neq + (neq if axi else 0) + (neq - 7) + (1 if ns else 0))
+    return {"k1a": 8.0 * k1a, "k1b": 8.0 * k1b, "k2": 8.0 * k2}
 
 
 def cpu_baseline(model):
@@ -265,7 +270,7 @@ def main():
     runner.solver.set_timing(False)
     if os.environ.get("HF2D_BENCH_RANKS") == "1":   # per-rank view: tile mix and the two timed launches
         print(f"[rank {rank}] tiles {runner.solver.tile_counts()} edge {runner.solver.edge_tile_counts()} active {act_local} "
-              f"s1_plain {kt['k1_plain_ms']:.3f} ms  s2_plain {kt['k2_plain_ms']:.3f} ms", file=sys.stderr, flush=True)
+              f"k1a {kt['k1a_plain_ms']:.3f} ms  k1b {kt['k1b_plain_ms']:.3f} ms  k2 {kt['k2_plain_ms']:.3f} ms", file=sys.stderr, flush=True)
     act = runner.allreduce_sum(act_local)
     value = act * K / (ms * 1e-3)
     bpc_step = runner.solver.bytes_per_cell()
@@ -274,13 +279,17 @@ def main():
         n_plain -= runner.solver.edge_tile_counts()[0]
     plain_cells = n_plain * tc * tr
     peak, peak_src = peaks()
-    b2 = stage2_bytes_per_cell(args.model)
-    t2 = kt["k2_plain_ms"] * 1e-3
-    achieved = b2 * plain_cells / t2 / 1e9 if t2 > 0 else 0.0
+    kb = kernel_bytes_per_cell(args.model)
+    kms = {"k1a": kt["k1a_plain_ms"], "k1b": kt["k1b_plain_ms"], "k2": kt["k2_plain_ms"]}
+    kname = {"k1a": "k_stage1_plain<plain tiles> (Stage 1 + blending factor)", "k1b": "k_point<plain tiles> (EOS, chemistry, tables, dt)",
+             "k2": "k_flux<plain tiles> (gradients, turbulence, fluxes)"}
+    kfrac = {q: (kb[q] * plain_cells / (kms[q] * 1e-3) / 1e9 / peak if kms[q] > 0 else 0.0) for q in kb}
+    top = max(kms, key=lambda q: kms[q])          # the dominant kernel = the longest of the three
+    achieved = kfrac[top] * peak
     traffic = None
-    try:   # DRAM bytes per plain cell of one k_stage2 launch, from the committed ncu capture (profiles/)
-        with open(os.path.join(ROOT, "profiles", "stage2_traffic.json")) as f:
-            traffic = json.load(f).get(args.model, {}).get("dram_bytes_per_plain_cell") * plain_cells
+    try:   # DRAM bytes per plain cell of that kernel, from the committed ncu capture (profiles/): a property of the profile, not of this run
+        with open(os.path.join(ROOT, "profiles", "kernel_traffic.json")) as f:
+            traffic = json.load(f).get(args.model, {}).get(top + "_dram_bytes_per_plain_cell") * plain_cells
     except Exception:
         pass
     step_gbs = bpc_step * act_local * K / (ms * 1e-3) / 1e9
@@ -292,9 +301,10 @@ def main():
                        "tiles_per_gpu": {"plain": n_plain, "general": n_gen, "cols": tc, "rows": tr},
                        "l2": "per-step working set (~6 GB/GPU) >> 126 MB L2: no flush needed", "parallelism": f"x-slab{world}"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                         "kernel": "k_stage2<plain tiles>", "bytes_per_cell": b2, "cells_per_launch": plain_cells,
-                         "kernel_ms": kt["k2_plain_ms"], "kernel_launches_timed": kt["launches"][1], "peak_source": peak_src,
-                         "k1_plain_ms": kt["k1_plain_ms"],
+                         "traffic_source": "profiles/kernel_traffic.json (ncu capture of the same command, not this run)" if traffic else None,
+                         "kernel": kname[top], "bytes_per_cell": kb[top], "cells_per_launch": plain_cells,
+                         "kernel_ms": kms[top], "kernel_launches_timed": kt["launches"][0], "peak_source": peak_src,
+                         "kernels": {q: {"ms": kms[q], "bytes_per_cell": kb[q], "frac": kfrac[q]} for q in kb},
                          "whole_step": {"bytes_per_active_cell": bpc_step, "achieved": step_gbs, "frac": step_gbs / peak}},
             "gpu_launches": int(runner.launches_last), "clocks": clocks}
     if rank == 0 and not args.no_cpu:

@@ -184,10 +184,10 @@ void* hf2d_gpu_stream(hf2d_gpu* h);   /* cudaStream_t the handle launches on */
 int  hf2d_gpu_set_stream(hf2d_gpu* h, void* cuda_stream);   /* launch on the caller's stream instead */
 int  hf2d_gpu_dt_export(hf2d_gpu* h, void* dev_double);     /* running dt minimum -> caller's device double */
 int  hf2d_gpu_dt_import(hf2d_gpu* h, const void* dev_double);
-/* per-kernel device time of the two plain-tile launches (slot 0 = Stage 1, slot 1 = Stage 2), CUDA events on the
- * launching stream; enable != 0 (re)starts the collection (at most 256 launches per slot are kept) */
+/* per-kernel device time of the three plain-tile launches (slot 0 = K1a k_stage1_plain, 1 = K1b k_point, 2 = K2 k_flux),
+ * CUDA events on the launching stream; enable != 0 (re)starts the collection (at most 256 launches per slot are kept) */
 int  hf2d_gpu_set_timing(hf2d_gpu* h, int enable);
-int  hf2d_gpu_get_timing(hf2d_gpu* h, double ms_mean[2], int count[2]);
+int  hf2d_gpu_get_timing(hf2d_gpu* h, double ms_mean[3], int count[3]);
 unsigned long long hf2d_gpu_launch_count(hf2d_gpu* h);      /* kernels launched through this handle so far */
 
 /* GlobalTime of the running output cycle.  The reference stamps it on every swept node (FlowNode2D::time,

@@ -299,9 +299,9 @@ class Solver:
         _ck(lib().hf2d_gpu_set_timing(self._h, int(enable)))
 
     def get_timing(self):
-        ms, cnt = (C.c_double * 2)(), (C.c_int * 2)()
+        ms, cnt = (C.c_double * 3)(), (C.c_int * 3)()
         _ck(lib().hf2d_gpu_get_timing(self._h, ms, cnt))
-        return {"k1_plain_ms": ms[0], "k2_plain_ms": ms[1], "launches": (cnt[0], cnt[1])}
+        return {"k1a_plain_ms": ms[0], "k1b_plain_ms": ms[1], "k2_plain_ms": ms[2], "launches": (cnt[0], cnt[1], cnt[2])}
 
     def launch_count(self) -> int:
         return int(lib().hf2d_gpu_launch_count(self._h))

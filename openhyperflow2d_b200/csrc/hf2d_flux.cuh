@@ -45,12 +45,15 @@ __global__ void __launch_bounds__(K2_THREADS, KC::plain ? K2_MINB_PLAIN : K2_MIN
 k_flux(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI, int want_grads) {
     const StepState st0 = *P.st;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int t_idx = blockIdx.x * K2_WARPS + warp;
+    // plain tiles: a warp walks the TI columns of its tile; general tiles: one column per warp (see k_point)
+    const int w_idx = blockIdx.x * K2_WARPS + warp;
+    const int t_idx = KC::plain ? w_idx : w_idx / TI;
     if (t_idx >= n_tiles) return;
     const int tile = tiles[t_idx];
     const int tx = tile / n_sb, sb = tile - tx * n_sb;
     const int j = sb * TILE_H + lane;
-    const int i0 = P.i_lo + tx * TI, i1 = min(i0 + TI, P.i_hi);
+    const int i0 = P.i_lo + tx * TI + (KC::plain ? 0 : w_idx - t_idx * TI);
+    const int i1 = min(KC::plain ? i0 + TI : i0 + 1, P.i_hi);
     const bool valid_j = j < P.ny;
     const long long ny = P.ny, N = P.N;
     const double yj = (KC::axi && valid_j) ? P.yrow[j] : 1.0;

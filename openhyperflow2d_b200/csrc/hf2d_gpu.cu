@@ -68,7 +68,7 @@ struct hf2d_gpu {
     bool s2_pending;                // Stage-2 parts queued, planes not yet swapped (hf2d_gpu_step_part S2_FINISH does)
     int plain_ttc;                  // TurbType word of the plain tiles (-1: no plain kernel for this grid)
     // optional per-kernel timing of the two plain-tile launches (bench.py roofline): event pairs on the main stream
-    bool timing; std::vector<cudaEvent_t> tev[2][2]; int tn[2];
+    bool timing; std::vector<cudaEvent_t> tev[3][2]; int tn[3];
     bool prepass_done;              // hf2d_gpu_step_prepass already ran for the current step
     double global_time; bool have_global_time;   // GlobalTime of the running cycle (hf2d_gpu_set_global_time): FlowNode2D::time at download
     int rms_every;                  // residual norms are reduced on steps with iter % rms_every == 0 and on the last step of a call
@@ -117,6 +117,12 @@ extern "C" int hf2d_gpu_create(const hf2d_cfg* cfg, int device, hf2d_gpu** out) 
         memset(&tabs[t], 0, sizeof(DevTable));
         tabs[t].n = cfg->tab[t].n;
         for (int r = 0; r < cfg->tab[t].n; r++) { tabs[t].x[r] = cfg->tab[t].x[r]; tabs[t].y[r] = cfg->tab[t].y[r]; }
+        {   // look-up class (hf2d_dev.cuh TAB_*)
+            const int n = tabs[t].n; const double* x = tabs[t].x;
+            bool asc = n >= 3;
+            for (int r = 1; r < n && asc; r++) asc = x[r - 1] < x[r];
+            tabs[t].cls = (n >= 2 && (n == 2 || x[0] >= x[n - 1])) ? TAB_ENDS : asc ? TAB_ASCENDING : TAB_SCAN;
+        }
     }
     if (dalloc(h, &h->d_tab, HF2D_NTABLES)) return HF2D_ECUDA;
     CK(cudaMemcpyAsync(h->d_tab, tabs.data(), sizeof(DevTable) * HF2D_NTABLES, cudaMemcpyHostToDevice, h->stream));
@@ -141,7 +147,7 @@ extern "C" int hf2d_gpu_create(const hf2d_cfg* cfg, int device, hf2d_gpu** out) 
     P.pow_cmu_34[0] = pow(0.09, 3. / 4.); P.pow_cmu_34[1] = pow(0.0845, 3. / 4.);
     P.tab = h->d_tab; P.st = h->d_st;
     h->last_iter_cycle = cfg->last_iter;
-    h->rms_every = cfg->NOutStep; h->prepass_done = false; h->timing = false; h->tn[0] = h->tn[1] = 0;
+    h->rms_every = cfg->NOutStep; h->prepass_done = false; h->timing = false; h->tn[0] = h->tn[1] = h->tn[2] = 0;
     h->TI = 16; h->n_sb = h->n_tx = 0; h->d_tiles_plain = h->d_tiles_gen = nullptr; h->n_plain = h->n_gen = 0; h->n_plain_edge = h->n_gen_edge = 0; h->s2_pending = false; h->n_chains_local = 0; h->d_nlist_seam = nullptr; h->n_nlist_seam = 0; h->prepass_local_done = false; h->ahead = false; h->plain_ttc = -1; h->keep_grads = true; h->grads_this_step = false; h->grads_valid = false;
     *out = h;
     return HF2D_OK;
@@ -156,7 +162,7 @@ extern "C" int hf2d_gpu_destroy(hf2d_gpu* h) {
     if (h->d_image) cudaFree(h->d_image);
     if (h->h_st) cudaFreeHost(h->h_st);
     cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
-    for (int a = 0; a < 2; a++) for (int b = 0; b < 2; b++) for (cudaEvent_t e : h->tev[a][b]) cudaEventDestroy(e);
+    for (int a = 0; a < 3; a++) for (int b = 0; b < 2; b++) for (cudaEvent_t e : h->tev[a][b]) cudaEventDestroy(e);
     cudaStreamDestroy(h->stream0); cudaStreamDestroy(h->stream_b); cudaStreamDestroy(h->stream_c); cudaEventDestroy(h->ev_fork_c); cudaEventDestroy(h->ev_join_c); cudaEventDestroy(h->ev_fork); cudaEventDestroy(h->ev_join);
     delete h;
     return HF2D_OK;

@@ -73,17 +73,24 @@ k_point(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI, 
     if (S2_SMEM_TABLES) smem_tables_fill(sh_tab, P.tab);
     const StepState st = *P.st;   // snapshot (the accumulators are only touched through atomics)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int t_idx = blockIdx.x * K1_WARPS + warp;
+    // plain tiles: a warp walks the TI columns of its tile; general tiles (few, latency-bound): one COLUMN per warp, so that
+    // the launch is TI times wider and its critical path TI times shorter (nothing is carried from column to column)
+    const int w_idx = blockIdx.x * K1_WARPS + warp;
+    const int t_idx = KC::plain ? w_idx : w_idx / TI;
     const int tile = t_idx < n_tiles ? tiles[t_idx] : 0;
     const int tx = tile / n_sb, sb = tile - tx * n_sb;
     const int j = sb * TILE_H + lane;
-    const int i0 = P.i_lo + tx * TI, i1 = t_idx < n_tiles ? min(i0 + TI, P.i_hi) : i0;
+    const int i0 = P.i_lo + tx * TI + (KC::plain ? 0 : w_idx - t_idx * TI);
+    const int i1 = t_idx < n_tiles ? min(KC::plain ? i0 + TI : i0 + 1, P.i_hi) : i0;
     const bool valid_j = j < P.ny;
     const long long ny = P.ny, N = P.N;
     if (threadIdx.x < K1_WARPS * 2 * NEQ) (&sh_acc[0][0])[threadIdx.x] = 0.;
     if (lane < 2 * NEQ) sh_u[warp][lane] = 0ull;
     __syncthreads();
     unsigned long long r_dt = ~0ull, r_err = ~0ull;
+    int trow[12];                  // row of the last look-up in each property table (tab_get_c)
+#pragma unroll
+    for (int q = 0; q < 12; q++) trow[q] = 1;
     const double dt = st.dt;
     const double dtdx = ddiv(dt, P.dx), dtdy = ddiv(dt, P.dy);                  // :843-844
     const double dyy = ddiv(P.dx, P.dx + P.dy), dxx = ddiv(P.dy, P.dx + P.dy);   // :643-644
@@ -285,14 +292,14 @@ k_point(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI, 
                     // A species whose mass fraction is exactly 0 contributes (+-)0 to the three sums below whatever its table
                     // says, so its lookups are skipped (identical result unless the whole sum is zero or Tg is not finite).
                     const bool h0 = L.Yfu != 0., h1 = L.Yox != 0., h2 = L.Ycp != 0., h3 = L.Yair != 0.;
-                    CP_new = (h0 ? tab_get_s(dv, sh_tab, tb, 0, L.Tg) : 0.) * L.Yfu + (h1 ? tab_get_s(dv, sh_tab, tb, 1, L.Tg) : 0.) * L.Yox +
-                             (h2 ? tab_get_s(dv, sh_tab, tb, 2, L.Tg) : 0.) * L.Ycp + (h3 ? tab_get_s(dv, sh_tab, tb, 3, L.Tg) : 0.) * L.Yair;
+                    CP_new = (h0 ? tab_get_c(dv, sh_tab, tb, 0, L.Tg, trow) : 0.) * L.Yfu + (h1 ? tab_get_c(dv, sh_tab, tb, 1, L.Tg, trow) : 0.) * L.Yox +
+                             (h2 ? tab_get_c(dv, sh_tab, tb, 2, L.Tg, trow) : 0.) * L.Ycp + (h3 ? tab_get_c(dv, sh_tab, tb, 3, L.Tg, trow) : 0.) * L.Yair;
                     if (KC::ns) {
-                        lam_new = (h0 ? tab_get_s(dv, sh_tab, tb, 4, L.Tg) : 0.) * L.Yfu + (h1 ? tab_get_s(dv, sh_tab, tb, 5, L.Tg) : 0.) * L.Yox +
-                                  (h2 ? tab_get_s(dv, sh_tab, tb, 6, L.Tg) : 0.) * L.Ycp + (h3 ? tab_get_s(dv, sh_tab, tb, 7, L.Tg) : 0.) * L.Yair;
+                        lam_new = (h0 ? tab_get_c(dv, sh_tab, tb, 4, L.Tg, trow) : 0.) * L.Yfu + (h1 ? tab_get_c(dv, sh_tab, tb, 5, L.Tg, trow) : 0.) * L.Yox +
+                                  (h2 ? tab_get_c(dv, sh_tab, tb, 6, L.Tg, trow) : 0.) * L.Ycp + (h3 ? tab_get_c(dv, sh_tab, tb, 7, L.Tg, trow) : 0.) * L.Yair;
                         have_lam = true;
-                        mu_new = (h0 ? tab_get_s(dv, sh_tab, tb, 8, L.Tg) : 0.) * L.Yfu + (h1 ? tab_get_s(dv, sh_tab, tb, 9, L.Tg) : 0.) * L.Yox +
-                                 (h2 ? tab_get_s(dv, sh_tab, tb, 10, L.Tg) : 0.) * L.Ycp + (h3 ? tab_get_s(dv, sh_tab, tb, 11, L.Tg) : 0.) * L.Yair;
+                        mu_new = (h0 ? tab_get_c(dv, sh_tab, tb, 8, L.Tg, trow) : 0.) * L.Yfu + (h1 ? tab_get_c(dv, sh_tab, tb, 9, L.Tg, trow) : 0.) * L.Yox +
+                                 (h2 ? tab_get_c(dv, sh_tab, tb, 10, L.Tg, trow) : 0.) * L.Ycp + (h3 ? tab_get_c(dv, sh_tab, tb, 11, L.Tg, trow) : 0.) * L.Yair;
                     }
                     s4 = L.y4; s5 = L.y5; s6 = L.y6;
                     if (sp) { for (int q = 0; q < 4; q++) sp->Yw[q] = L.Y[q]; }

@@ -44,33 +44,49 @@ __device__ __forceinline__ void k1a_item(const Params& P, const StepState& st, i
     const bool edge = lane == 0 || lane == 31;
     const long long eo = lane == 0 ? -1 : 1;                  // lane 0: the row below the tile, lane 31: the row above
     for (int cb = 0; cb < TI; cb += K1A_COLS) {
-        const int nc = min(K1A_COLS, TI - cb);
+        const int nc = min(K1A_COLS, TI - cb);        // (= K1A_COLS for the default tile width: the predicates below are uniform)
         const long long n0 = n_first + (long long)cb * ny;        // node of column 0 of the batch
-        // ---- every load of the batch, before the first use ----
+        // ---- every load of the batch, before the first use (plain pointer walks: one 64-bit add per column and plane) ----
         double s[K1A_COLS + 2], a[K1A_COLS + 2], b[K1A_COLS], be[K1A_COLS], se[K1A_COLS], bedge[K1A_COLS];
         double sr[K1A_COLS], dsu[K1A_COLS], bm2[K1A_COLS], fax[K1A_COLS];
+        {
+            const double* __restrict__ ps = Sk + (n0 - ny);
+            const double* __restrict__ pa = Ak + (n0 - ny);
 #pragma unroll
-        for (int c = 0; c < K1A_COLS + 2; c++) {
-            s[c] = 0.; a[c] = 0.;
-            if (c < nc + 2) { s[c] = Sk[n0 + (long long)(c - 1) * ny]; a[c] = Ak[n0 + (long long)(c - 1) * ny]; }
-        }
+            for (int c = 0; c < K1A_COLS + 2; c++) {
+                s[c] = 0.; a[c] = 0.;
+                if (c < nc + 2) { s[c] = *ps; a[c] = *pa; }
+                ps += ny; pa += ny;
+            }
+            const double* __restrict__ pb = Bk + n0;
+            const double* __restrict__ pbe = betak + n0;
+            const double* __restrict__ pse = Sk + (n0 + eo);
+            const double* __restrict__ pbd = Bk + (n0 + eo);
+            const double* __restrict__ psr = has_src ? P.Src + ((long long)K * N + n0) : nullptr;
+            const double* __restrict__ pds = (f & 16) ? P.dSy_in[K] + (n0 + 1) : nullptr;
+            const double* __restrict__ pfx = KC::axi ? P.F + ((long long)K * N + n0) : nullptr;
 #pragma unroll
-        for (int c = 0; c < K1A_COLS; c++) {
-            b[c] = be[c] = sr[c] = se[c] = bedge[c] = dsu[c] = bm2[c] = fax[c] = 0.;
-            if (c < nc) {
-                const long long n = n0 + (long long)c * ny;
-                b[c] = Bk[n]; be[c] = betak[n];
-                if (has_src) sr[c] = P.Src[(long long)K * N + n];
-                if (edge) { se[c] = Sk[n + eo]; bedge[c] = Bk[n + eo]; }
-                if (f & 16) { dsu[c] = P.dSy_in[K][n + 1]; bm2[c] = Bk[n - 2]; }
-                if (KC::axi) fax[c] = P.F[(long long)K * N + n];
+            for (int c = 0; c < K1A_COLS; c++) {
+                b[c] = be[c] = sr[c] = se[c] = bedge[c] = dsu[c] = bm2[c] = fax[c] = 0.;
+                if (c < nc) {
+                    b[c] = *pb; be[c] = *pbe;
+                    if (has_src) sr[c] = *psr;
+                    if (edge) { se[c] = *pse; bedge[c] = *pbd; }
+                    if (f & 16) { dsu[c] = *pds; bm2[c] = pb[-2]; }
+                    if (KC::axi) fax[c] = *pfx;
+                }
+                pb += ny; pbe += ny; pse += ny; pbd += ny;
+                if (has_src) psr += ny;
+                if (f & 16) pds += ny;
+                if (KC::axi) pfx += ny;
             }
         }
         // ---- Stage 1 + blending factor, column by column ----
+        long long n = n0 - ny;
 #pragma unroll
         for (int c = 0; c < K1A_COLS; c++) {
             if (c >= nc) break;
-            const long long n = n0 + (long long)c * ny;
+            n += ny;
             const double sc = s[c + 1], sl = s[c], srr = s[c + 2];
             double su = __shfl_down_sync(0xffffffffu, sc, 1), sd = __shfl_up_sync(0xffffffffu, sc, 1);
             double bu = __shfl_down_sync(0xffffffffu, b[c], 1), bd = __shfl_up_sync(0xffffffffu, b[c], 1);
