@@ -6,6 +6,7 @@
 #include "hf2d_stage1.cuh"
 #include "hf2d_point.cuh"
 #include "hf2d_stage1_plain.cuh"
+#include "hf2d_stage1_tma.cuh"
 #include "hf2d_flux.cuh"
 #include "hf2d_heat.cuh"
 
@@ -72,6 +73,8 @@ struct hf2d_gpu {
     bool prepass_done;              // hf2d_gpu_step_prepass already ran for the current step
     double global_time; bool have_global_time;   // GlobalTime of the running cycle (hf2d_gpu_set_global_time): FlowNode2D::time at download
     int rms_every;                  // residual norms are reduced on steps with iter % rms_every == 0 and on the last step of a call
+    // TMA tile staging of K1a (hf2d_stage1_tma.cuh): tensor maps of the per-equation planes; off when the grid cannot be addressed
+    K1aMaps maps; K1aMaps* d_maps; bool tma_ok; const double* S_half0; const double* dSy8_half0;
     bool keep_grads;                // hf2d_gpu_keep_gradients: the last step of every step call writes the 18 gradient planes
     bool grads_this_step, grads_valid;
 };
@@ -148,7 +151,7 @@ extern "C" int hf2d_gpu_create(const hf2d_cfg* cfg, int device, hf2d_gpu** out) 
     P.tab = h->d_tab; P.st = h->d_st;
     h->last_iter_cycle = cfg->last_iter;
     h->rms_every = cfg->NOutStep; h->prepass_done = false; h->timing = false; h->tn[0] = h->tn[1] = h->tn[2] = 0;
-    h->TI = 16; h->n_sb = h->n_tx = 0; h->d_tiles_plain = h->d_tiles_gen = nullptr; h->n_plain = h->n_gen = 0; h->n_plain_edge = h->n_gen_edge = 0; h->s2_pending = false; h->n_chains_local = 0; h->d_nlist_seam = nullptr; h->n_nlist_seam = 0; h->prepass_local_done = false; h->ahead = false; h->plain_ttc = -1; h->keep_grads = true; h->grads_this_step = false; h->grads_valid = false;
+    h->TI = 16; h->n_sb = h->n_tx = 0; h->d_tiles_plain = h->d_tiles_gen = nullptr; h->n_plain = h->n_gen = 0; h->n_plain_edge = h->n_gen_edge = 0; h->s2_pending = false; h->n_chains_local = 0; h->d_nlist_seam = nullptr; h->n_nlist_seam = 0; h->prepass_local_done = false; h->ahead = false; h->plain_ttc = -1; h->tma_ok = false; h->d_maps = nullptr; h->S_half0 = nullptr; h->dSy8_half0 = nullptr; h->keep_grads = true; h->grads_this_step = false; h->grads_valid = false;
     *out = h;
     return HF2D_OK;
 }
@@ -174,6 +177,58 @@ static int ensure_grad_planes(hf2d_gpu* h) {
     if (h->P.grad || !h->P.ns) return 0;
     if (dalloc(h, &h->P.grad, (size_t)G_COUNT * h->P.N)) return HF2D_ECUDA;
     return 0;
+}
+// ---- tensor maps for the TMA unit (driver entry point fetched through the runtime: no link against libcuda) ----
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                    const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static PFN_encodeTiled tma_encoder() {
+    static PFN_encodeTiled fn = nullptr; static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* p = nullptr; cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess) fn = (PFN_encodeTiled)p;
+        else cudaGetLastError();
+    }
+    return fn;
+}
+// planes of nx*ny doubles, `nplanes` of them N apart (rank 3) or one plane (rank 2); box = rows x cols (x 1 plane)
+static bool tma_map(CUtensorMap* m, const double* base, int nx, int ny, int nplanes, int box_rows, int box_cols) {
+    PFN_encodeTiled enc = tma_encoder();
+    if (!enc || !base) return false;
+    const cuuint64_t dims[3] = {(cuuint64_t)ny, (cuuint64_t)nx, (cuuint64_t)nplanes};
+    const cuuint64_t strides[2] = {(cuuint64_t)ny * 8, (cuuint64_t)nx * (cuuint64_t)ny * 8};
+    const cuuint32_t box[3] = {(cuuint32_t)box_rows, (cuuint32_t)box_cols, 1};
+    const cuuint32_t es[3] = {1, 1, 1};
+    const int rank = nplanes > 1 ? 3 : 2;
+    return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, (cuuint32_t)rank, (void*)base, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+// after the planes are allocated (hf2d_gpu_upload_aos): K1a's tensor maps; any failure leaves the LDG kernel in charge
+static void build_tma_maps(hf2d_gpu* h) {
+    const Params& P = h->P;
+    h->tma_ok = false;
+    const char* off = getenv("HF2D_NO_TMA");
+    if (off && off[0] == '1') return;
+    if (h->TI != K1T_TI || (P.ny & 1) || h->n_plain == 0) return;       // TMA strides are multiples of 16 bytes
+    memset(&h->maps, 0, sizeof(h->maps));
+    const double* s0 = P.S_in < P.S_out ? P.S_in : P.S_out;
+    h->S_half0 = s0;
+    bool ok = tma_map(&h->maps.S[0], s0, P.nx, P.ny, NEQ, K1T_S_ROWS, K1T_TI + 2) && tma_map(&h->maps.S[1], s0 + (long long)NEQ * P.N, P.nx, P.ny, NEQ, K1T_S_ROWS, K1T_TI + 2) &&
+              tma_map(&h->maps.A, P.A, P.nx, P.ny, NEQ, 32, K1T_TI + 2) && tma_map(&h->maps.B, P.B, P.nx, P.ny, NEQ, K1T_B_ROWS, K1T_TI) &&
+              tma_map(&h->maps.beta, P.beta, P.nx, P.ny, NEQ, 32, K1T_TI);
+    if (ok && P.Src) ok = tma_map(&h->maps.Src, P.Src, P.nx, P.ny, NEQ, 32, K1T_TI);
+    if (ok && P.F) ok = tma_map(&h->maps.F, P.F, P.nx, P.ny, NEQ, 32, K1T_TI);
+    h->dSy8_half0 = nullptr;
+    if (ok && P.dSy_in[8]) {
+        const double* d0 = P.dSy_in[8] < P.dSy_out[8] ? P.dSy_in[8] : P.dSy_out[8];
+        h->dSy8_half0 = d0;
+        ok = tma_map(&h->maps.dSy[0], d0, P.nx, P.ny, 1, K1T_DS_ROWS, K1T_TI) && tma_map(&h->maps.dSy[1], d0 + P.N, P.nx, P.ny, 1, K1T_DS_ROWS, K1T_TI);
+    }
+    if (ok) {
+        if (dalloc(h, &h->d_maps, 1)) { cudaGetLastError(); return; }
+        if (cudaMemcpyAsync(h->d_maps, &h->maps, sizeof(K1aMaps), cudaMemcpyHostToDevice, h->stream) != cudaSuccess || cudaStreamSynchronize(h->stream) != cudaSuccess) { cudaGetLastError(); return; }
+    }
+    h->tma_ok = ok;
 }
 extern "C" int hf2d_gpu_keep_gradients(hf2d_gpu* h, int enable) {
     if (!h) return fail(HF2D_EINVAL, "null");
