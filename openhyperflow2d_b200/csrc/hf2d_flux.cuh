@@ -86,6 +86,27 @@ k_flux(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI, i
         NbState mine;
         mine.rho = mine.y4 = mine.y5 = mine.y6 = mine.s7 = mine.s8 = mine.U = mine.V = mine.Tg = 0.;
         if (valid_j) nb_load(P.S_out, P.U_out, P.V_out, P.Tg_out, N, n, turbN, mine);
+#if K_PREFETCH
+        if constexpr (KC::plain) {
+            if (i + 1 < i1) {      // the next column's operands, requested under this column's arithmetic
+                const long long m = n + ny;
+#pragma unroll
+                for (int k = 0; k < 7; k++) pf(&P.S_out[(long long)k * N + m]);
+                if (TURB_C) { pf(&P.S_out[7 * N + m]); pf(&P.S_out[8 * N + m]); }
+                pf(&P.U_out[m]); pf(&P.V_out[m]); pf(&P.Tg_out[m]); pf(&P.p_out[m]); pf(&P.kg_out[m]);
+                pf(&P.SN[4 * N + m]); pf(&P.SN[5 * N + m]); pf(&P.SN[6 * N + m]);
+                if (KC::ns) {
+                    pf(&P.CP_in[m]); pf(&P.R_in[m]); pf(&P.mu_in[m]); pf(&P.kg_in[m]); pf(&P.mu_t[m]); pf(&P.lam_in[m]);
+                    if (KC::ttc != 0) pf(&P.l_min[m]);
+                    // its right neighbour's old state (its up neighbour's lies in the lines this column touches as `right`)
+                    const long long r = m + ny;
+                    pf(&P.S_in[r]); pf(&P.S_in[4 * N + r]); pf(&P.S_in[5 * N + r]); pf(&P.S_in[6 * N + r]);
+                    if (TURB_C) { pf(&P.S_in[7 * N + r]); pf(&P.S_in[8 * N + r]); }
+                    pf(&P.U_in[r]); pf(&P.V_in[r]); pf(&P.Tg_in[r]);
+                }
+            }
+        }
+#endif
         // down neighbour's new state: lane-1 holds it as its own; lane 0 reads the row below the tile
         NbState nD;
         nD.rho = shfl_up1(mine.rho); nD.y4 = shfl_up1(mine.y4); nD.y5 = shfl_up1(mine.y5); nD.y6 = shfl_up1(mine.y6);

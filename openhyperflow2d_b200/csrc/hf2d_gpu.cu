@@ -74,7 +74,7 @@ struct hf2d_gpu {
     double global_time; bool have_global_time;   // GlobalTime of the running cycle (hf2d_gpu_set_global_time): FlowNode2D::time at download
     int rms_every;                  // residual norms are reduced on steps with iter % rms_every == 0 and on the last step of a call
     // TMA tile staging of K1a (hf2d_stage1_tma.cuh): tensor maps of the per-equation planes; off when the grid cannot be addressed
-    K1aMaps maps; K1aMaps* d_maps; bool tma_ok; const double* S_half0; const double* dSy8_half0;
+    K1aMaps maps; K1aMaps* d_maps; bool tma_ok; bool k1t_all_big; const double* S_half0; const double* dSy8_half0;
     bool keep_grads;                // hf2d_gpu_keep_gradients: the last step of every step call writes the 18 gradient planes
     bool grads_this_step, grads_valid;
 };
@@ -151,7 +151,7 @@ extern "C" int hf2d_gpu_create(const hf2d_cfg* cfg, int device, hf2d_gpu** out) 
     P.tab = h->d_tab; P.st = h->d_st;
     h->last_iter_cycle = cfg->last_iter;
     h->rms_every = cfg->NOutStep; h->prepass_done = false; h->timing = false; h->tn[0] = h->tn[1] = h->tn[2] = 0;
-    h->TI = 16; h->n_sb = h->n_tx = 0; h->d_tiles_plain = h->d_tiles_gen = nullptr; h->n_plain = h->n_gen = 0; h->n_plain_edge = h->n_gen_edge = 0; h->s2_pending = false; h->n_chains_local = 0; h->d_nlist_seam = nullptr; h->n_nlist_seam = 0; h->prepass_local_done = false; h->ahead = false; h->plain_ttc = -1; h->tma_ok = false; h->d_maps = nullptr; h->S_half0 = nullptr; h->dSy8_half0 = nullptr; h->keep_grads = true; h->grads_this_step = false; h->grads_valid = false;
+    h->TI = 16; h->n_sb = h->n_tx = 0; h->d_tiles_plain = h->d_tiles_gen = nullptr; h->n_plain = h->n_gen = 0; h->n_plain_edge = h->n_gen_edge = 0; h->s2_pending = false; h->n_chains_local = 0; h->d_nlist_seam = nullptr; h->n_nlist_seam = 0; h->prepass_local_done = false; h->ahead = false; h->plain_ttc = -1; h->tma_ok = false; h->k1t_all_big = false; h->d_maps = nullptr; h->S_half0 = nullptr; h->dSy8_half0 = nullptr; h->keep_grads = true; h->grads_this_step = false; h->grads_valid = false;
     *out = h;
     return HF2D_OK;
 }
@@ -209,6 +209,7 @@ static void build_tma_maps(hf2d_gpu* h) {
     h->tma_ok = false;
     const char* off = getenv("HF2D_NO_TMA");
     if (off && off[0] == '1') return;
+    { const char* e = getenv("HF2D_K1T_ALL_BIG"); h->k1t_all_big = e && e[0] == '1'; }   // (tests: every equation through the full-stage launch)
     if (h->TI != K1T_TI || (P.ny & 1) || h->n_plain == 0) return;       // TMA strides are multiples of 16 bytes
     memset(&h->maps, 0, sizeof(h->maps));
     const double* s0 = P.S_in < P.S_out ? P.S_in : P.S_out;

@@ -43,6 +43,9 @@ template <int NS, int AXI, int TTC> struct KCfg {
     static constexpr bool plain = TTC >= 0;
 };
 
+#ifndef K1B_LAZY
+#define K1B_LAZY 0                // 1: plain tiles fetch last step's U, V, Tg, p only where FillNode2D returns early (32 B/cell less, but the dependent branch costs more than the bytes: 0.444 vs 0.416 ms)
+#endif
 // Where a node's own inputs come from: last step's planes.
 struct GlobalLoad {
     const Params& P; long long m;
@@ -70,14 +73,20 @@ __device__ __forceinline__ void local_rest(D& dv, const LD& ld, const Params& P,
     // NT_FC nodes always run FillNode2D(1,0,...) (deeps2d_core.cpp:1331), active nodes follow TurbStartIter (:1240-1244)
     const int is_init = fc ? 0 : st.is_init;
     L.s7c = L.S[7]; L.s8c = L.S[8];
-    L.Uo = ld.U(); L.Vo = ld.V(); L.Tgo = ld.Tg();
-    L.U = L.Uo; L.V = L.Vo; L.Tg = L.Tgo;
-    L.Ut = L.Uo; L.Vt = L.Vo;
     L.CP = ld.CP(); L.R = ld.R();
     L.mu = KC::ns ? ld.mu() : 0.;
     const double kg_old = ld.kg();
     L.kg = kg_old;
-    if (FULL) { L.po = ld.p(); L.p = L.po; }
+    // Last step's U, V, Tg, p survive only where FillNode2D returns early (S[Rho] == 0 or k < 1) or a CONST flag pins them:
+    // an unflagged interior node overwrites all four, so the plain-tile kernels fetch them only in the early-return case
+    // (4 planes = 32 B per cell that the bulk of the grid never reads).
+    if (!KC::plain || !K1B_LAZY || (L.S[iRho] == 0) || (kg_old < 1)) {
+        L.Uo = ld.U(); L.Vo = ld.V(); L.Tgo = ld.Tg();
+        if (FULL) L.po = ld.p();
+    } else { L.Uo = L.Vo = L.Tgo = 0.; if (FULL) L.po = 0.; }
+    L.U = L.Uo; L.V = L.Vo; L.Tg = L.Tgo;
+    L.Ut = L.Uo; L.Vt = L.Vo;
+    if (FULL) L.p = L.po;
     if (!act && !fc) { L.y4 = L.S[4]; L.y5 = L.S[5]; L.y6 = L.S[6]; return; }
     // ---- FillNode2D, local part (hyper_flow_node.hpp:382-492) ----
     if (!(L.S[iRho] == 0) && !(kg_old < 1)) {

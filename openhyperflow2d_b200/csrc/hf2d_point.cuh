@@ -137,6 +137,17 @@ k_point(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI, 
             // plain tiles: K1a (k_stage1_plain) has written NextNode->S and the new blending factors, equation by equation
 #pragma unroll
             for (int k = 0; k < NE_C; k++) if (valid_j) sn[k] = P.SN[(long long)k * N + n];
+#if K_PREFETCH
+            if (i + 1 < i1) {          // the next column's operands, requested under this column's arithmetic
+                const long long m = n + ny;
+#pragma unroll
+                for (int k = 0; k < NE_C; k++) pf(&P.SN[(long long)k * N + m]);
+                if (NE_C < 9 && TURB_C) pf(&P.S_in[8 * N + m]);
+                pf(&P.CP_in[m]); pf(&P.R_in[m]); pf(&P.kg_in[m]);
+                if (!K1B_LAZY) { pf(&P.U_in[m]); pf(&P.V_in[m]); pf(&P.Tg_in[m]); pf(&P.p_in[m]); }
+                if (KC::ns) { pf(&P.mu_in[m]); if (KC::ttc & TCT_k_eps_Model) pf(&P.l_min[m]); }
+            }
+#endif
         } else if (act) {
             const int n1 = (tt & TT_IDXL) ? 1 : 0, n2 = (tt & TT_IDXR) ? 1 : 0, n3 = (tt & TT_IDYU) ? 1 : 0, n4 = (tt & TT_IDYD) ? 1 : 0;
             const long long nL = n - n1 * ny, nR = n + n2 * ny, nU = n + n3, nD = n - n4;

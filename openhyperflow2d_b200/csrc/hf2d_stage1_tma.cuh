@@ -36,14 +36,27 @@ struct K1aMaps {                 // tensor maps of one grid (hf2d_gpu_upload_aos
 #define K1T_DS_ROWS 34                // dSdy of the eps equation: rows j0 .. j0+33, read at row j+1
 #define K1T_OFF_X1 K1T_ALIGN128(K1T_OFF_X0 + 32 * K1T_TI * 8)                  // dSdy (eps) or F
 #define K1T_OFF_X2 K1T_ALIGN128(K1T_OFF_X1 + K1T_DS_ROWS * K1T_TI * 8)          // F when dSdy is there too
-#define K1T_STAGE_BYTES K1T_ALIGN128(K1T_OFF_X2 + 32 * K1T_TI * 8)             // 16128
+#define K1T_STAGE_BYTES K1T_ALIGN128(K1T_OFF_X2 + 32 * K1T_TI * 8)             // 16128: every optional box present
+#define K1T_STAGE_BYTES_SMALL K1T_OFF_X0                                       // 9856: S, A, B, beta only (equations 0..6 of a flat grid without sources)
 #ifndef K1T_WARPS
 #define K1T_WARPS 4
 #endif
 #define K1T_THREADS (32 * K1T_WARPS)
-#define K1T_SMEM (K1T_WARPS * K1T_STAGE_BYTES + 64)
-#ifndef K1T_MINB
-#define K1T_MINB 3
+#define K1T_STAGE_OF(big, axi) ((big) ? ((axi) ? K1T_STAGE_BYTES : K1T_OFF_X2) : K1T_STAGE_BYTES_SMALL)   // flat grids have no F box: 14208
+#define K1T_SMEM_OF(big, axi) (K1T_WARPS * K1T_STAGE_OF(big, axi) + 64)
+// Two launch shapes.  The stage of a warp is what limits residency (bytes in flight AND warps to cover the FP64 dependent-issue
+// latency of the blending-factor divisions): 7 of the 9 equations of a flat k-eps grid need only the four basic boxes (9.9 KB),
+// so they run in a launch of their own with 5 blocks = 20 warps per SM and ONE code path for all seven (the equation index
+// is a run-time plane offset: a third of the instruction footprint, the per-k switch had 13 % instruction-cache stalls);
+// the equations with Src / dSdy / F boxes keep the larger stage (14 KB flat: 4 blocks = 16 warps per SM; 16 KB axisymmetric: 3 blocks) and the compile-time switch.
+#ifndef K1T_MINB_BIG
+#define K1T_MINB_BIG(axi) ((axi) ? 3 : 4)
+#endif
+#ifndef K1T_MINB_SMALL
+#define K1T_MINB_SMALL 5
+#endif
+#ifndef K1T_BATCH
+#define K1T_BATCH 4               // columns whose blending-factor divisions run as one branch-free block
 #endif
 
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
@@ -65,9 +78,12 @@ __device__ __forceinline__ void tma_load_2d(unsigned dst, const CUtensorMap* map
 }
 
 // the arithmetic of one staged item, equation index compile-time (as k1a_item, operands from shared memory)
-template <class KC, int K>
+// (KT = -1: equations 0..6 of a grid without Src / F planes -- identical flags, the index kk is a run-time plane offset)
+template <class KC, int KT>
 __device__ __forceinline__ void k1t_item(const Params& P, const StepState& st, const unsigned char* __restrict__ stage, int lane, int j, long long n_first,
-                                         int want_rms, K1aAcc& acc) {
+                                         int want_rms, K1aAcc& acc, int kk) {
+    constexpr int KF = KT < 0 ? 0 : KT;             // flags of equations 0..6 of an unflagged node are all "advance | ddx | ddy"
+    const int K = KT < 0 ? kk : KT;
     constexpr uint32_t ct = CT_NODE_IS_SET, tt = (uint32_t)KC::ttc | TT_IDXL | TT_IDXR | TT_IDYU | TT_IDYD;
     const long long ny = P.ny, N = P.N;
     const double dt = st.dt;
@@ -75,9 +91,11 @@ __device__ __forceinline__ void k1t_item(const Params& P, const StepState& st, c
     const double dyy = ddiv(P.dx, P.dx + P.dy), dxx = ddiv(P.dy, P.dx + P.dy);   // :643-644
     double* __restrict__ betak = P.beta + (long long)K * N;
     double* __restrict__ SNk = P.SN + (long long)K * N;
-    constexpr unsigned f = eq_flags_c(ct, tt, K, KC::ns);
-    const bool has_src = K >= 7 || P.has_src;
-    const bool trk_x = (P.need_dsx >> K) & 1u, trk_y = (P.need_dsy >> K) & 1u;
+    constexpr unsigned f = eq_flags_c(ct, tt, KF, KC::ns);
+    static_assert(KT >= 0 || (f == 7u && !KC::axi), "run-time equation index: plain flags, flat grid");
+    const bool has_src = KT < 0 ? false : (KT >= 7 || P.has_src);
+    // (the run-time-index launch is only used when no dS plane of equations 0..6 is tracked: hf2d_step.inc)
+    const bool trk_x = KT < 0 ? false : ((P.need_dsx >> KF) & 1u) != 0, trk_y = KT < 0 ? false : ((P.need_dsy >> KF) & 1u) != 0;
     constexpr bool DY2 = (f & 16) != 0;
     const double* __restrict__ sS = reinterpret_cast<const double*>(stage + K1T_OFF_S) + lane;      // row j-2 of column i0-1
     const double* __restrict__ sA = reinterpret_cast<const double*>(stage + K1T_OFF_A) + lane;      // row j   of column i0-1
@@ -86,46 +104,65 @@ __device__ __forceinline__ void k1t_item(const Params& P, const StepState& st, c
     const double* __restrict__ sSrc = reinterpret_cast<const double*>(stage + K1T_OFF_X0) + lane;
     const double* __restrict__ sDs = reinterpret_cast<const double*>(stage + K1T_OFF_X1) + lane;
     const double* __restrict__ sF = reinterpret_cast<const double*>(stage + (DY2 ? K1T_OFF_X2 : K1T_OFF_X1)) + lane;
-    long long n = n_first - ny;
+    // Columns in batches of K1T_BATCH: first every column's Stage-1 value (straight-line, independent), then the residual /
+    // blending-factor divisions of the whole batch as ONE branch-free block with a single validity vote behind it, so that
+    // the 2 divisions + 1 square root of K1T_BATCH columns overlap (each is a dependent chain of ~12 FP64 instructions;
+    // with 3 warps per scheduler resident a column-by-column vote left the FP64 pipe waiting on one chain at a time).
+    const double beta_min = OMIN(P.beta0, st.beta_scn);
+    const double bb = beta_min * beta_min;
 #pragma unroll
-    for (int c = 0; c < K1T_TI; c++) {
-        n += ny;
-        const double sc = sS[(c + 1) * K1T_S_ROWS + 2], sl = sS[c * K1T_S_ROWS + 2], srr = sS[(c + 2) * K1T_S_ROWS + 2];
-        const double su = sS[(c + 1) * K1T_S_ROWS + 3], sd = sS[(c + 1) * K1T_S_ROWS + 1];
-        const double bu = sB[c * K1T_B_ROWS + 3], bd = sB[c * K1T_B_ROWS + 1];
-        const double beta = sBe[c * 32], _beta = 1. - beta;
-        double dXX = 0., dYY = 0.;
-        if (f & 2) dXX = (sA[(c + 2) * 32] - sA[c * 32]) * 0.5;
-        if (f & 4) dYY = (bu - bd) * 0.5;
-        if (trk_x) P.dSx_out[K][n] = dXX;
-        if (trk_y) P.dSy_out[K][n] = dYY;
-        if (DY2) {   // :1011-1013: up = last step's dSdy, down = this sweep's (the row below is an unflagged interior node too)
-            const double dd = (sB[c * K1T_B_ROWS + 2] - sB[c * K1T_B_ROWS]) * 0.5;
-            dYY = (sDs[c * K1T_DS_ROWS + 1] + dd) * 0.5;
+    for (int cb = 0; cb < K1T_TI; cb += K1T_BATCH) {
+        double scv[K1T_BATCH], vv[K1T_BATCH], bev[K1T_BATCH];
+        bool any_res = false;
+#pragma unroll
+        for (int q = 0; q < K1T_BATCH; q++) {
+            const int c = cb + q;
+            const long long n = n_first + (long long)c * ny;
+            const double sc = sS[(c + 1) * K1T_S_ROWS + 2], sl = sS[c * K1T_S_ROWS + 2], srr = sS[(c + 2) * K1T_S_ROWS + 2];
+            const double su = sS[(c + 1) * K1T_S_ROWS + 3], sd = sS[(c + 1) * K1T_S_ROWS + 1];
+            const double bu = sB[c * K1T_B_ROWS + 3], bd = sB[c * K1T_B_ROWS + 1];
+            const double beta = sBe[c * 32], _beta = 1. - beta;
+            double dXX = 0., dYY = 0.;
+            if (f & 2) dXX = (sA[(c + 2) * 32] - sA[c * 32]) * 0.5;
+            if (f & 4) dYY = (bu - bd) * 0.5;
+            if (trk_x) P.dSx_out[KF][n] = dXX;
+            if (trk_y) P.dSy_out[KF][n] = dYY;
+            if (DY2) {   // :1011-1013: up = last step's dSdy, down = this sweep's (the row below is an unflagged interior node too)
+                const double dd = (sB[c * K1T_B_ROWS + 2] - sB[c * K1T_B_ROWS]) * 0.5;
+                dYY = (sDs[c * K1T_DS_ROWS + 1] + dd) * 0.5;
+            }
+            const double src = has_src ? sSrc[c * 32] : 0.;
+            double v;
+            if (KC::axi) v = sc * beta + _beta * (dxx * (sl + srr) + dyy * (su + sd)) * 0.5 - (dtdx * dXX + dtdy * (dYY + ddiv(sF[c * 32], (double)(j + 1)))) + src * dt + 0.;
+            else v = sc * beta + _beta * (dxx * (sl + srr) + dyy * (su + sd)) * 0.5 - (dtdx * dXX + dtdy * dYY) + src * dt + 0.;
+            SNk[n] = v;
+            scv[q] = sc; vv[q] = v; bev[q] = beta;
+            any_res |= sc != 0.;
         }
-        const double src = has_src ? sSrc[c * 32] : 0.;
-        double v;
-        if (KC::axi) v = sc * beta + _beta * (dxx * (sl + srr) + dyy * (su + sd)) * 0.5 - (dtdx * dXX + dtdy * (dYY + ddiv(sF[c * 32], (double)(j + 1)))) + src * dt + 0.;
-        else v = sc * beta + _beta * (dxx * (sl + srr) + dyy * (su + sd)) * 0.5 - (dtdx * dXX + dtdy * dYY) + src * dt + 0.;
-        SNk[n] = v;
         // residual + blending factor (:1062-1154)
-        const bool res = sc != 0.;
-        if (__any_sync(0xffffffffu, res)) {
-            const double beta_min = OMIN(P.beta0, st.beta_scn);
-            const double bb = beta_min * beta_min;
-            double DD = 0., newb = 0.;
-            auto ph = [&](auto& dv) {
+        if (!__any_sync(0xffffffffu, any_res)) continue;
+        double DDv[K1T_BATCH], newb[K1T_BATCH];
+        auto ph = [&](auto& dv) {
+#pragma unroll
+            for (int q = 0; q < K1T_BATCH; q++) {
+                const bool res = scv[q] != 0.;
                 double sqrt_RES;
-                DD = residual_dd(dv, sc, v, res, sqrt_RES, P.bFF);
-                const double xx = (P.bFF >= 4) ? sqrt_RES : (P.bFF >= 2) ? DD * DD : DD;
-                const double cap = (P.bFF & 1) ? (beta_min + beta) * 0.5 : beta_min;
+                DDv[q] = residual_dd(dv, scv[q], vv[q], res, sqrt_RES, P.bFF);
+                const double xx = (P.bFF >= 4) ? sqrt_RES : (P.bFF >= 2) ? DDv[q] * DDv[q] : DDv[q];
+                const double cap = (P.bFF & 1) ? (beta_min + bev[q]) * 0.5 : beta_min;
                 const double quo = dv.div(bb, beta_min + xx, res);
-                newb = OMIN(cap, quo);
-            };
-            if (want_rms) { DivExact e; ph(e); }
-            else { DivFast fdv; ph(fdv); if (__any_sync(0xffffffffu, fdv.is_bad())) { DivExact e; ph(e); } }
-            if (res) betak[n] = newb;
+                newb[q] = OMIN(cap, quo);
+            }
+        };
+        if (want_rms) { DivExact e; ph(e); }
+        else { DivFast fdv; ph(fdv); if (__any_sync(0xffffffffu, fdv.is_bad())) { DivExact e; ph(e); } }
+#pragma unroll
+        for (int q = 0; q < K1T_BATCH; q++) {
+            const bool res = scv[q] != 0.;
+            const long long n = n_first + (long long)(cb + q) * ny;
+            if (res) betak[n] = newb[q];
             if (want_rms && res) {
+                const double sc = scv[q], v = vv[q], DD = DDv[q];
                 if (P.isAlternateRMS) { acc.div += sc * sc; acc.rms += v - sc; } else { acc.rms += DD * DD; }
                 acc.cnt++;
                 if (DD != DD) atomicMax(&P.st->nan_last[K], (unsigned long long)n + 1ull);
@@ -135,22 +172,27 @@ __device__ __forceinline__ void k1t_item(const Params& P, const StepState& st, c
     }
 }
 
-template <class KC>
-__global__ void __launch_bounds__(K1T_THREADS, K1T_MINB)
-k_stage1_tma(Params P, const K1aMaps* __restrict__ Mp, const int* __restrict__ tiles, int n_tiles, int n_sb, int s_half, int ds_half, int want_rms) {
+// BIG = false: equations [k_first, k_first + k_count) within 0..6, four-box stage, run-time equation index;
+// BIG = true:  any equations, full stage, compile-time switch.
+template <class KC, bool BIG>
+__global__ void __launch_bounds__(K1T_THREADS, BIG ? K1T_MINB_BIG(KC::axi) : K1T_MINB_SMALL)
+k_stage1_tma(Params P, const K1aMaps* __restrict__ Mp, const int* __restrict__ tiles, int n_tiles, int n_sb, int s_half, int ds_half, int want_rms,
+             int k_first, int k_count) {
     static_assert(KC::plain, "plain tiles only");
     constexpr int NE_C = !KC::ns ? 7 : (KC::ttc & TCT_Prandtl_Model) ? 7 : (KC::ttc & TCT_k_eps_Model) ? 9 : (KC::ttc & TCT_SA_Model) ? 8 : 7;
     constexpr uint32_t ct = CT_NODE_IS_SET, tt = (uint32_t)KC::ttc | TT_IDXL | TT_IDXR | TT_IDYU | TT_IDYD;
+    constexpr int STAGE = K1T_STAGE_OF(BIG, KC::axi);
     extern __shared__ __align__(128) unsigned char k1t_smem[];
     const StepState st = *P.st;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    unsigned char* stage = k1t_smem + (size_t)warp * K1T_STAGE_BYTES;
-    const unsigned bar = smem_u32(k1t_smem + (size_t)K1T_WARPS * K1T_STAGE_BYTES + 8 * warp);
-    // item = k * n_tiles + t: the warps of a block work on vertically adjacent tiles of the same plane set
+    unsigned char* stage = k1t_smem + (size_t)warp * STAGE;
+    const unsigned bar = smem_u32(k1t_smem + (size_t)K1T_WARPS * STAGE + 8 * warp);
+    // item = (k - k_first) * n_tiles + t: the warps of a block work on vertically adjacent tiles of the same plane set
     const long long item = (long long)blockIdx.x * K1T_WARPS + warp;
-    const bool in_range = item < (long long)n_tiles * NE_C;
-    const int k = in_range ? (int)(item / n_tiles) : 0;
-    const int tile = in_range ? tiles[(int)(item - (long long)k * n_tiles)] : 0;
+    const bool in_range = item < (long long)n_tiles * k_count;
+    const int kq = in_range ? (int)(item / n_tiles) : 0;
+    const int k = k_first + kq;
+    const int tile = in_range ? tiles[(int)(item - (long long)kq * n_tiles)] : 0;
     const int tx = tile / n_sb, sb = tile - tx * n_sb;
     const int j0 = sb * TILE_H, j = j0 + lane;
     const int i0 = P.i_lo + tx * K1T_TI;
@@ -160,34 +202,40 @@ k_stage1_tma(Params P, const K1aMaps* __restrict__ Mp, const int* __restrict__ t
         if (lane == 0) {
             mbar_init(bar, 1);
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-            const bool has_src = k >= 7 || P.has_src;
-            const bool dy2 = (eq_flags(ct, tt, k, KC::ns) & 16) != 0;
+            const bool has_src = BIG && (k >= 7 || P.has_src);
+            const bool dy2 = BIG && (eq_flags(ct, tt, k, KC::ns) & 16) != 0;
             unsigned bytes = (K1T_S_ROWS * (K1T_TI + 2) + 32 * (K1T_TI + 2) + K1T_B_ROWS * K1T_TI + 32 * K1T_TI) * 8;
             if (has_src) bytes += 32 * K1T_TI * 8;
             if (dy2) bytes += K1T_DS_ROWS * K1T_TI * 8;
-            if (KC::axi) bytes += 32 * K1T_TI * 8;
+            if (BIG && KC::axi) bytes += 32 * K1T_TI * 8;
             mbar_expect_tx(bar, bytes);
             const unsigned sbase = smem_u32(stage);
             tma_load_3d(sbase + K1T_OFF_S, &Mp->S[s_half], bar, j0 - 2, i0 - 1, k);
             tma_load_3d(sbase + K1T_OFF_A, &Mp->A, bar, j0, i0 - 1, k);
             tma_load_3d(sbase + K1T_OFF_B, &Mp->B, bar, j0 - 2, i0, k);
             tma_load_3d(sbase + K1T_OFF_BETA, &Mp->beta, bar, j0, i0, k);
-            if (has_src) tma_load_3d(sbase + K1T_OFF_X0, &Mp->Src, bar, j0, i0, k);
-            if (dy2) tma_load_2d(sbase + K1T_OFF_X1, &Mp->dSy[ds_half], bar, j0, i0);
-            if (KC::axi) tma_load_3d(sbase + (dy2 ? K1T_OFF_X2 : K1T_OFF_X1), &Mp->F, bar, j0, i0, k);
+            if constexpr (BIG) {
+                if (has_src) tma_load_3d(sbase + K1T_OFF_X0, &Mp->Src, bar, j0, i0, k);
+                if (dy2) tma_load_2d(sbase + K1T_OFF_X1, &Mp->dSy[ds_half], bar, j0, i0);
+                if (KC::axi) tma_load_3d(sbase + (dy2 ? K1T_OFF_X2 : K1T_OFF_X1), &Mp->F, bar, j0, i0, k);
+            }
         }
         __syncwarp();
         mbar_wait(bar, 0);
-        switch (k) {
-        case 0: k1t_item<KC, 0>(P, st, stage, lane, j, n_first, want_rms, acc); break;
-        case 1: k1t_item<KC, 1>(P, st, stage, lane, j, n_first, want_rms, acc); break;
-        case 2: k1t_item<KC, 2>(P, st, stage, lane, j, n_first, want_rms, acc); break;
-        case 3: k1t_item<KC, 3>(P, st, stage, lane, j, n_first, want_rms, acc); break;
-        case 4: k1t_item<KC, 4>(P, st, stage, lane, j, n_first, want_rms, acc); break;
-        case 5: k1t_item<KC, 5>(P, st, stage, lane, j, n_first, want_rms, acc); break;
-        case 6: k1t_item<KC, 6>(P, st, stage, lane, j, n_first, want_rms, acc); break;
-        case 7: if constexpr (NE_C > 7) k1t_item<KC, 7>(P, st, stage, lane, j, n_first, want_rms, acc); break;
-        case 8: if constexpr (NE_C > 8) k1t_item<KC, 8>(P, st, stage, lane, j, n_first, want_rms, acc); break;
+        if constexpr (!BIG) {
+            if constexpr (!KC::axi) k1t_item<KC, -1>(P, st, stage, lane, j, n_first, want_rms, acc, k);
+        } else {
+            switch (k) {
+            case 0: k1t_item<KC, 0>(P, st, stage, lane, j, n_first, want_rms, acc, 0); break;
+            case 1: k1t_item<KC, 1>(P, st, stage, lane, j, n_first, want_rms, acc, 1); break;
+            case 2: k1t_item<KC, 2>(P, st, stage, lane, j, n_first, want_rms, acc, 2); break;
+            case 3: k1t_item<KC, 3>(P, st, stage, lane, j, n_first, want_rms, acc, 3); break;
+            case 4: k1t_item<KC, 4>(P, st, stage, lane, j, n_first, want_rms, acc, 4); break;
+            case 5: k1t_item<KC, 5>(P, st, stage, lane, j, n_first, want_rms, acc, 5); break;
+            case 6: k1t_item<KC, 6>(P, st, stage, lane, j, n_first, want_rms, acc, 6); break;
+            case 7: if constexpr (NE_C > 7) k1t_item<KC, 7>(P, st, stage, lane, j, n_first, want_rms, acc, 7); break;
+            case 8: if constexpr (NE_C > 8) k1t_item<KC, 8>(P, st, stage, lane, j, n_first, want_rms, acc, 8); break;
+            }
         }
     }
     if (want_rms) {      // uniform per launch

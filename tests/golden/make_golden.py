@@ -265,6 +265,76 @@ def bc_cases():
     return B
 
 
+def r2_cases():
+    """Round-2 additions (tests/golden/r2/): what the earlier fixtures left unpinned.
+    * burning decks: the earlier "reacting" decks put their fuel jet on a SingleBound, which the reference applies BEFORE
+      the contour bounds (deeps2d_core.cpp:3417-3517 vs :3520-3800) -- the contour's inflow face then overwrites it and no
+      fuel ever enters.  Here the inflow face of the contour itself is split into a hot fuel segment and a hot oxidiser
+      segment, so both arms of CalcChemicalReactions (:4711-4722) fire, products form and the fuel / product rows of the
+      property tables are evaluated;
+    * grids tall enough (ny >= 100) to hold PLAIN tiles (32-row strips with an unflagged ring), for the kernel
+      instantiations the 60x40 / 96x64 cases never reach: axisymmetric, Prandtl, Smagorinsky, Euler, laminar, SA;
+    * N = 200 drift cases, one per physics family that survives 200 steps in the reference."""
+    R = {}
+    # ---- burning jets, 60 x 40 (general tiles) ----
+    nx, ny, dx, dy = 60, 40, 1e-3, 1e-3
+    X, Y = nx * dx, ny * dy
+    split = [(0.0, Y), (X - 1e-5, Y), (X - 1e-5, 0.0), (0.0, 0.0), (0.0, 0.012)]
+    fl = [air(1.5, p=101350., T=1400., comp=1), air(comp=1, T=1400.), air(1.2, p=101350., T=1100., comp=0)]
+    eb = [("NT_D0Y_2D", 1), ("NT_D0X_2D", 1), ("NT_AX_2D", 1), ("NT_FC_2D", 3), ("NT_FC_2D", 1)]
+    R["axi_burn_euler"] = dict(deck=dict(problem=0, flow_type=1, flows=fl, bounds=eb, contour=split,
+                                         areas=[{"seed": (5, 20), "type": 1, "flow": 1}], tf=900., k0=8.0), steps=[12])
+    kb = [("NT_D0Y_2D, TCT_dkdy_NULL_2D, TCT_depsdy_NULL_2D", 1), ("NT_D0X_2D, TCT_dkdx_NULL_2D, TCT_depsdx_NULL_2D", 1),
+          ("NT_AX_2D, TCT_dkdy_NULL_2D, TCT_depsdy_NULL_2D", 1), ("NT_FC_2D, TCT_k_CONST_2D, TCT_eps_CONST_2D", 3),
+          ("NT_FC_2D, TCT_k_CONST_2D, TCT_eps_CONST_2D", 1)]
+    R["axi_burn_keps"] = dict(deck=dict(problem=1, flow_type=1, turb=4, turb_ext=4, turb_reset=1, turb_start=1, flows=fl, bounds=kb,
+                                        contour=split, areas=[{"seed": (5, 20), "type": 1, "flow": 1}], tf=900., k0=2000.0), steps=[10])
+    # flat, laminar, fuel-rich core initialised in the field (Area with the fuel state) burning against an air co-flow
+    flf = [air(2.0, p=101350., T=1300., comp=1), air(comp=1), air(1.5, p=101350., T=1200., comp=0)]
+    nb = [("NT_D0Y_2D", 1), ("NT_D0X_2D", 1), ("NT_D0Y_2D", 1), ("NT_FC_2D", 3), ("NT_FC_2D", 1)]
+    R["flat_burn_laminar"] = dict(deck=dict(problem=1, turb=0, flows=flf, bounds=nb, contour=split,
+                                            areas=[{"seed": (5, 20), "type": 1, "flow": 1}], tf=1000., k0=500.), steps=[10])
+    # ---- grids that hold PLAIN tiles: 40 x 100 (two 32-row strips x three 8-column tiles with an unflagged ring) ----
+    nx, ny = 40, 100
+    X, Y = nx * dx, ny * dy
+    geo = wedge_geometry(nx, ny, dx, dy, 0.024, 0.011)
+    areas = [{"seed": (3, 3), "type": 1, "flow": 1}, {"seed": (nx - 3, 2), "type": 0, "mat": 1}]
+    big = dict(nx=nx, ny=ny, contour=geo, areas=areas)
+    ns_b = [("NT_FARFIELD_2D", 1), ("NT_D0X_2D, CT_NONREFLECTED_2D", 1), ("NT_WNS_2D", 2), ("NT_D0Y_2D, CT_V_CONST_2D", 2), ("NT_FARFIELD_2D", 1)]
+    euler_b = [("NT_FC_2D", 1), ("NT_D0X_2D", 1), ("NT_D0Y_2D, CT_V_CONST_2D", 2), ("NT_D0Y_2D, CT_V_CONST_2D", 2), ("NT_FC_2D", 1)]
+    R["plain_euler"] = dict(deck=dict(problem=0, flows=[air(2.5), air()], bounds=euler_b, bff=2, **big), steps=[8])
+    R["plain_ns_laminar"] = dict(deck=dict(problem=1, turb=0, flows=[air(2.5), air()], bounds=ns_b, **big), steps=[8])
+    R["plain_ns_prandtl_vd"] = dict(deck=dict(problem=1, turb=2, turb_ext=1, turb_start=0, flows=[air(2.5), air()], bounds=ns_b, bff=5, **big), steps=[8])
+    R["plain_ns_smagorinsky"] = dict(deck=dict(problem=1, turb=5, turb_ext=15, turb_start=0, flows=[air(2.5), air()], bounds=ns_b, **big), steps=[8])
+    plate = [(0.0, Y), (X - 1e-5, Y), (X - 1e-5, 0.0), (0.0, 0.0)]
+    sa_b = [("NT_FARFIELD_2D, TCT_k_CONST_2D", 1), ("NT_D0X_2D, TCT_dkdx_NULL_2D, CT_NONREFLECTED_2D", 1), ("NT_WNS_2D", 2),
+            ("NT_FARFIELD_2D, TCT_k_CONST_2D", 1)]
+    R["plain_ns_sa_subsonic"] = dict(deck=dict(nx=nx, ny=ny, problem=1, turb=3, turb_ext=10, turb_reset=1, turb_start=1, flows=[air(0.5), air()],
+                                               bounds=sa_b, contour=plate, areas=[{"seed": (5, 20), "type": 1, "flow": 1}]), steps=[4])
+    # odd ny: the TMA path is not eligible (16-byte stride rule), the LDG form of K1a runs
+    geo_o = wedge_geometry(nx, 101, dx, dy, 0.024, 0.011)
+    ke_b = [("NT_FARFIELD_2D, TCT_k_CONST_2D, TCT_eps_CONST_2D", 1),
+            ("NT_D0X_2D, TCT_dkdx_NULL_2D, TCT_depsdx_NULL_2D,  CT_NONREFLECTED_2D", 1),
+            ("NT_WNS_2D, TCT_eps_Cmk2kXn_WALL_2D", 2),
+            ("NT_D0Y_2D, TCT_dkdy_NULL_2D, TCT_depsdy_NULL_2D, CT_V_CONST_2D", 2),
+            ("NT_FARFIELD_2D, TCT_k_CONST_2D, TCT_eps_CONST_2D", 1)]
+    R["plain_ns_keps_odd_ny"] = dict(deck=dict(nx=nx, ny=101, problem=1, turb=4, turb_ext=4, turb_reset=1, turb_start=1, adiabatic=0,
+                                               flows=[air(2.5), air()], bounds=ke_b, contour=geo_o, areas=areas), steps=[8])
+    # axisymmetric burning jets on the tall grid: config C5's plain-tile kernels (KCfg<*, 1, *>)
+    split_b = [(0.0, Y), (X - 1e-5, Y), (X - 1e-5, 0.0), (0.0, 0.0), (0.0, 0.040)]
+    R["plain_axi_burn_euler"] = dict(deck=dict(nx=nx, ny=ny, problem=0, flow_type=1, flows=fl, bounds=eb, contour=split_b,
+                                               areas=[{"seed": (5, 50), "type": 1, "flow": 1}], tf=900., k0=2000.0), steps=[10])
+    R["plain_axi_burn_keps"] = dict(deck=dict(nx=nx, ny=ny, problem=1, flow_type=1, turb=4, turb_ext=4, turb_reset=1, turb_start=1, flows=fl,
+                                              bounds=kb, contour=split_b, areas=[{"seed": (5, 50), "type": 1, "flow": 1}], tf=900., k0=2000.0), steps=[10])
+    R["plain_axi_burn_laminar"] = dict(deck=dict(nx=nx, ny=ny, problem=1, flow_type=1, turb=0, flows=fl, bounds=eb, contour=split_b,
+                                                 areas=[{"seed": (5, 50), "type": 1, "flow": 1}], tf=900., k0=40.0), steps=[10])
+    # ---- drift over 200 steps (SURVEY section 4): the 60 x 40 ramp duct of cases() ----
+    C = cases()
+    for name in ("euler_duct", "ns_laminar", "ns_keps_std", "ns_prandtl_vd"):
+        R["drift_" + name] = dict(deck=C[name]["deck"], steps=[200])
+    return R
+
+
 def restart_cases():
     """Runs RESTARTED from the swap file of an earlier run of the same deck (`restart_after` steps): the reference's
     start-up then computes y_plus from real wall gradients (Recalc_y_plus, hf2d_start.cpp:299) -- in a fresh run they are
@@ -298,7 +368,9 @@ def main(only=None):
     os.makedirs(os.path.join(HERE, "bc"), exist_ok=True)
     todo = ([(c, s, HERE) for c, s in cases().items()] + [(c, s, os.path.join(HERE, "geometry")) for c, s in geometry_cases().items()]
             + [(c, s, os.path.join(HERE, "bc")) for c, s in bc_cases().items()]
-            + [(c, s, os.path.join(HERE, "restart")) for c, s in restart_cases().items()])
+            + [(c, s, os.path.join(HERE, "restart")) for c, s in restart_cases().items()]
+            + [(c, s, os.path.join(HERE, "r2")) for c, s in r2_cases().items()])
+    os.makedirs(os.path.join(HERE, "r2"), exist_ok=True)
     os.makedirs(os.path.join(HERE, "restart"), exist_ok=True)
     for cname, spec, outdir in todo:
         if only and cname not in only and os.path.basename(outdir) + "/" + cname not in only:

@@ -30,6 +30,12 @@ def restart_case_names():
     return sorted("restart/" + os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "restart", "*.npz")))
 
 
+def r2_case_names():
+    """Round-2 fixtures (tests/golden/r2/): burning decks with fuel and products present, grids that hold plain tiles
+    (axisymmetric / Prandtl / Smagorinsky / SA / odd ny), 200-step drift cases."""
+    return sorted("r2/" + os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "r2", "*.npz")))
+
+
 def load_case(name):
     z = np.load(os.path.join(GOLDEN, *name.split("/")) + ".npz")
     cfg = config.parse_cfg(str(z["cfg"]))

@@ -5,10 +5,10 @@ import numpy as np
 import pytest
 
 import oracle_py as O
-from golden_util import STEP_FIELDS, bc_case_names, case_names, geometry_case_names, load_case, restart_case_names
+from golden_util import STEP_FIELDS, bc_case_names, case_names, geometry_case_names, load_case, r2_case_names, restart_case_names
 
 
-@pytest.mark.parametrize("name", case_names() + geometry_case_names() + bc_case_names() + restart_case_names())
+@pytest.mark.parametrize("name", case_names() + geometry_case_names() + bc_case_names() + restart_case_names() + r2_case_names())
 def test_oracle_matches_reference(name):
     c = load_case(name)
     cfg = c["cfg"]

@@ -20,7 +20,11 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 so = os.path.join(ROOT, "openhyperflow2d_b200", "libhf2d_gpu.so")
 
 fn, _, sub = kname.partition("@")
-out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", "regex:" + fn], capture_output=True, text=True).stdout
+if rep.endswith(".csv.gz"):      # a source page exported on the GPU box (tools/prof_plain.sh): every captured kernel, one block each
+    import gzip
+    out = gzip.open(rep, "rt").read()
+else:
+    out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", "regex:" + fn], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
 # several launches may follow each other: take the first block whose demangled name holds `sub`
 k_i = next(i for i, r in enumerate(rows) if r and r[0] == "Kernel Name" and sub in r[1])

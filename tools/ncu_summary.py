@@ -4,7 +4,7 @@ usage: tools/ncu_summary.py <report.ncu-rep> [cells_per_launch]"""
 import csv, io, subprocess, sys
 rep = sys.argv[1]
 cells = float(sys.argv[2]) if len(sys.argv) > 2 else None
-out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+out = open(rep).read() if rep.endswith(".csv") else subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout   # (a raw page exported on the GPU box)
 rows = list(csv.reader(io.StringIO(out)))
 hdr, units = rows[0], rows[1]
 idx = {h: i for i, h in enumerate(hdr)}
