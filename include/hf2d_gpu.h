@@ -224,6 +224,20 @@ int  hf2d_gpu_set_min_distance_to_wall(hf2d_gpu* h, const int* wall_ij, int n_wa
 int  hf2d_gpu_set_min_distance_to_wall_slab(hf2d_gpu* h, const int* wall_ij, int n_wall, int i_off, int nx_total,
                                             double* l_min, int* i_wall, int* j_wall, unsigned char* status);
 
+/* The same pass for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  NO COUNTERPART IN THE REFERENCE.  Allocates nothing --
+ * no cudaMalloc / cudaFree, no allocating library routine: the wall list is staged in a file-scope device array of
+ * HF2D_NOALLOC_MAX_WALLS = 16384 (i, j) pairs (128 KB that every GPU loading the library holds until exit); longer lists are
+ * refused with HF2D_EINVAL.  wall_ij is HOST memory as above; the four result planes are DEVICE buffers of the caller, nx*ny
+ * entries each, none NULL, same contents as the host planes of hf2d_gpu_set_min_distance_to_wall (bit for bit); the device
+ * l_min plane of the handle is updated in place.  One array per GPU shared by all calls: it keeps the last call's list
+ * (each call overwrites what its kernel reads), and calls that OVERLAP on one GPU race on it -- the call returns after its
+ * kernel has finished, so calls issued one after the other are safe.  The first call on a device resolves the array's address
+ * (cudaGetSymbolAddress); make one call before a region in which even that is unwelcome. */
+#define HF2D_NOALLOC_MAX_WALLS 16384
+int  hf2d_gpu_wall_distance_noalloc(hf2d_gpu* h, const int* wall_ij, int n_wall, double x0,
+                                    double* dev_l_min, int* dev_i_wall, int* dev_j_wall, unsigned char* dev_status);
+
 /* Raw residual accumulators of the last step that reduced them -- RMS(k,ii), sumDiv(k,ii), iRMS(k,ii) and the largest
  * |dS/S| of ONE sub-domain (deeps2d_core.cpp:1122-1153), HF2D_NEQ entries each, any pointer may be NULL.  A multi-GPU
  * driver all-reduces them over its X-slabs (SUM, SUM, SUM, MAX) and finishes the norms once (:1539-1574 with a single

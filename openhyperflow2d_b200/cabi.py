@@ -65,7 +65,8 @@ EXPORTS = ["hf2d_gpu_last_error", "hf2d_gpu_device_count", "hf2d_gpu_create", "h
            "hf2d_gpu_step_prepass", "hf2d_gpu_step_stage1", "hf2d_gpu_step_stage2", "hf2d_gpu_step_end", "hf2d_gpu_dt_ptr", "hf2d_gpu_stream",
            "hf2d_gpu_set_stream", "hf2d_gpu_set_timing", "hf2d_gpu_get_timing", "hf2d_gpu_dt_export", "hf2d_gpu_dt_import", "hf2d_gpu_launch_count",
            "hf2d_gpu_step_part", "hf2d_gpu_lane_fork", "hf2d_gpu_lane_join", "hf2d_gpu_side_stream", "hf2d_gpu_halo_pack_lane",
-           "hf2d_gpu_halo_unpack_lane", "hf2d_gpu_edge_tile_counts", "hf2d_gpu_set_min_distance_to_wall", "hf2d_gpu_set_global_time", "hf2d_gpu_recalc_y_plus", "hf2d_gpu_residual_sums", "hf2d_gpu_set_min_distance_to_wall_slab", "hf2d_gpu_keep_gradients"]
+           "hf2d_gpu_halo_unpack_lane", "hf2d_gpu_edge_tile_counts", "hf2d_gpu_set_min_distance_to_wall", "hf2d_gpu_set_global_time", "hf2d_gpu_recalc_y_plus", "hf2d_gpu_residual_sums", "hf2d_gpu_set_min_distance_to_wall_slab", "hf2d_gpu_keep_gradients",
+           "hf2d_gpu_wall_distance_noalloc"]
 
 
 def lib():
@@ -121,6 +122,7 @@ def lib():
                                                         C.c_void_p, C.c_void_p]
         L.hf2d_gpu_launch_count.restype = C.c_ulonglong
         L.hf2d_gpu_keep_gradients.argtypes = [C.c_void_p, C.c_int]
+        L.hf2d_gpu_wall_distance_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 
@@ -339,6 +341,12 @@ class Solver:
         _ck(lib().hf2d_gpu_set_min_distance_to_wall_slab(self._h, walls.ctypes.data, len(walls), int(i_off), int(nx_total),
                                                          l_min.ctypes.data, i_wall.ctypes.data, j_wall.ctypes.data, status.ctypes.data))
         return l_min, i_wall, j_wall, status
+
+    def wall_distance_noalloc(self, walls, dev_l_min: int, dev_i_wall: int, dev_j_wall: int, dev_status: int, x0: float = 0.0):
+        """hf2d_gpu_wall_distance_noalloc: the same pass without any allocation; the four result planes are DEVICE pointers
+        (nx*ny doubles / int32 / int32 / uint8) of the caller.  At most 16384 wall nodes."""
+        walls = np.ascontiguousarray(walls, dtype=np.int32).reshape(-1, 2)
+        _ck(lib().hf2d_gpu_wall_distance_noalloc(self._h, walls.ctypes.data, len(walls), float(x0), dev_l_min, dev_i_wall, dev_j_wall, dev_status))
 
     def set_min_distance_to_wall(self, walls, x0: float = 0.0):
         """SetMinDistanceToWall2D(J, WallNodes, x0) on the uploaded grid (deeps2d_core.cpp:4783-4832).  walls: (n, 2) int

@@ -239,3 +239,4 @@ extern "C" int hf2d_gpu_keep_gradients(hf2d_gpu* h, int enable) {
 #include "hf2d_io.inc"
 #include "hf2d_step.inc"
 #include "hf2d_walldist.inc"
+#include "hf2d_noalloc.inc"
