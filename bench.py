@@ -238,6 +238,9 @@ def main():
     ap.add_argument("--rms-every", type=int, default=100, help="NOutStep: residual norms reduced every n-th step and on the last one")
     ap.add_argument("--e2e-steps", type=int, default=500,
                     help="steps per output cycle (Nmax) of the end-to-end leg; the reference's own decks use 500 (TriplePoint.dat) to 24000 (Step.dat)")
+    ap.add_argument("--driver", default="c", choices=["c", "python"],
+                    help="N>1: the C X-slab driver (direct stores into the neighbours' HBM; default) or the torch.distributed/NCCL protocol harness")
+    ap.add_argument("--e2e-cycles", type=int, default=3, help="end-to-end cycles timed; the median is reported")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
@@ -257,7 +260,17 @@ def main():
         import torch.distributed as dist
         opts = dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)   # seam traffic must not queue behind the bulk kernels
         dist.init_process_group("nccl", device_id=torch.device("cuda", local), pg_options=opts)
-    runner = SlabRunner(args.nx, args.ny, model=args.model, rank=rank, world=world, device=local, seams=args.seams, rms_every=args.rms_every, schedule=args.schedule)
+    parity = None
+    use_c = world > 1 and args.driver == "c"
+    if use_c:
+        from openhyperflow2d_b200.multigpu import CSlabRunner, slab_parity_check
+        # driver-side evidence that the multi-GPU path is exact: a small grid on all N GPUs vs the single-domain run, before timing
+        ok = torch.tensor([1 if slab_parity_check(rank, world, local, model=args.model) else 0], dtype=torch.int64, device=torch.device("cuda", local))
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        parity = ("bit-exact" if int(ok.item()) == 1 else "MISMATCH") + f" (192x160 {args.model}, 7 steps, {world} X-slabs on {world} GPUs through the C slab driver vs the single-domain run; every rank's owned columns)"
+        runner = CSlabRunner(args.nx, args.ny, model=args.model, rank=rank, world=world, device=local, rms_every=args.rms_every)
+    else:
+        runner = SlabRunner(args.nx, args.ny, model=args.model, rank=rank, world=world, device=local, seams=args.seams, rms_every=args.rms_every, schedule=args.schedule)
     act_local, tot_local = runner.active_cells()
     W, K = max(args.warmup, 3), args.steps
     runner.step(W)
@@ -298,6 +311,7 @@ def main():
             "config": {"workload": f"BASELINE configs[3]: three cylinders, NS k-eps URANS (9 equations), flat, {args.nx}x{args.ny} cells per GPU "
                                    f"({args.nx * world}x{args.ny} total), X-slabs", "model": args.model,
                        "active_cells": act, "total_cells": args.nx * args.ny * world, "seams": args.seams, "schedule": args.schedule if world > 1 else None, "rms_every": args.rms_every,
+                       "multi_gpu_driver": (None if world == 1 else "C slab driver: peer-memory mailboxes over NVLink (hf2d_slab_run)" if use_c else "python SlabProtocol over NCCL"),
                        "tiles_per_gpu": {"plain": n_plain, "general": n_gen, "cols": tc, "rows": tr},
                        "l2": "per-step working set (~6 GB/GPU) >> 126 MB L2: no flush needed", "parallelism": f"x-slab{world}"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
@@ -309,9 +323,18 @@ def main():
             "gpu_launches": int(runner.launches_last), "clocks": clocks}
     if rank == 0 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(args.model)
+    if parity is not None:
+        line["parity"] = parity
     if not args.no_e2e:
-        e2e = runner.e2e_cycle(args.e2e_steps)
-        line["e2e"] = e2e
+        if use_c:
+            secs = runner.e2e_cycles(args.e2e_steps, cycles=args.e2e_cycles)
+        else:
+            secs = [runner.e2e_cycle(args.e2e_steps, cycles=1)["seconds"] for _ in range(max(1, args.e2e_cycles))]
+        med = sorted(secs)[len(secs) // 2]
+        line["e2e"] = {"value": act * args.e2e_steps / med, "unit": UNIT, "h2d_bytes_per_step": int(runner.J.nbytes / args.e2e_steps),
+                       "d2h_bytes_per_step": int(runner.J.nbytes / args.e2e_steps), "steps_per_cycle": args.e2e_steps, "cycles_run": len(secs),
+                       "seconds_per_cycle": secs, "seconds": med,
+                       "note": "median cycle: pinned host AoS image -> HBM (scanned + unpacked there), nsteps steps (= Nmax, one output cycle), packed into the resident image -> host; per-GPU bytes"}
     if rank == 0:
         print(json.dumps(line))
     runner.close()

@@ -255,6 +255,41 @@ int  hf2d_gpu_residual_sums(hf2d_gpu* h, double rms[HF2D_NEQ], double sum_div[HF
  * without walls: the reference then reads node (0,0)'s gradients, which are not kept); y+ of those nodes is unchanged. */
 int  hf2d_gpu_recalc_y_plus(hf2d_gpu* h, const int* i_wall, const int* j_wall, double* y_plus);
 
+/* ---------------------------------------------------------------------------------------------------------------------
+ * X-slab multi-GPU driver (csrc/hf2d_slab.inc).  Replaces, for the GPU path, the reference's multi-rank contract:
+ *   DEEPS2D_Run(o_stream, pJ, pC, rank, last_rank, x0)          libDEEPS2D/deeps2d_core.hpp:206-212, call hf2d_start.cpp:285
+ *   sub-domains cut from J by active-node count                 ScanArea, deeps2d_core.cpp:2153, 2207-2216; hf2d_start.cpp:149-175
+ *   ghost-column exchange, dt all-reduce, Var_pack gather       deeps2d_core.cpp:1336-1400, 806-809, 1402-1463
+ * One hf2d_slab per GPU.  Ghost columns travel by direct stores into the neighbour's HBM over NVLink (peer memory), each hop
+ * one pack+store+signal kernel and one wait+unpack kernel; no host round trip, no library collective on the step path.
+ * Usage (one process, N GPUs):  hf2d_slab_cuts -> N x hf2d_slab_create -> hf2d_slab_connect_local -> N x hf2d_slab_upload(J)
+ *                               -> hf2d_slab_run(all, N, nsteps, 1, &rep) per output cycle -> N x hf2d_slab_download(J).
+ *       (one process per GPU):  hf2d_slab_create(rank) -> hf2d_slab_ipc_handle -> all-gather the handles by any side channel
+ *                               -> hf2d_slab_connect_ipc -> upload -> hf2d_slab_run(&mine, 1, ...) on every rank.
+ * Results equal the single-GPU run of the undivided grid bit for bit (seams are exact: DESIGN.md section 5). */
+typedef struct hf2d_slab hf2d_slab;
+/* cuts[0..world]: slab r owns global columns [cuts[r], cuts[r+1]); (nearly) equal ACTIVE nodes per slab, every column owned */
+int  hf2d_slab_cuts(const void* J, const hf2d_node_layout* layout, int nx, int ny, int world, int min_cols, int* cuts);
+/* cfg_global describes the UNDIVIDED grid (nx = MaxX of the whole grid; rank / n_ranks are ignored) */
+int  hf2d_slab_create(const hf2d_cfg* cfg_global, int device, int rank, int world, const int* cuts, hf2d_slab** out);
+int  hf2d_slab_destroy(hf2d_slab* s);
+hf2d_gpu* hf2d_slab_solver(hf2d_slab* s);                  /* the slab's single-GPU handle (tile counts, timing, field pointers ...) */
+int  hf2d_slab_columns(hf2d_slab* s, int* c0, int* c1, int* ghost_left, int* ghost_right);
+size_t hf2d_slab_ipc_handle_bytes(void);                   /* 64 */
+int  hf2d_slab_ipc_handle(hf2d_slab* s, void* out);        /* this rank's mailbox, exportable to other processes */
+int  hf2d_slab_connect_ipc(hf2d_slab* s, const void* handles /* world x hf2d_slab_ipc_handle_bytes(), rank order */);
+int  hf2d_slab_connect_local(hf2d_slab* const* all, int world);   /* every rank in this process: peer access + raw pointers */
+/* J_global = the undivided host image; each slab reads its column range (+ ghost columns) and writes back ONLY its owned columns */
+int  hf2d_slab_upload(hf2d_slab* s, const void* J_global, const hf2d_node_layout* layout, int pinned);
+int  hf2d_slab_download(hf2d_slab* s, void* J_global, const hf2d_node_layout* layout, int pinned);
+/* the same with the slab's own image (ghost columns included) for callers that never hold the undivided grid */
+int  hf2d_slab_upload_local(hf2d_slab* s, const void* J_slab, const hf2d_node_layout* layout, int pinned);
+int  hf2d_slab_download_local(hf2d_slab* s, void* J_slab, const hf2d_node_layout* layout, int pinned);
+/* nsteps steps on the slabs this process drives (all ranks, or one); new_cycle as hf2d_gpu_step (1) / _step_continue (0).
+ * The report is the undivided grid's (whole-grid residual norms; dt, time global). */
+int  hf2d_slab_run(hf2d_slab* const* local, int n_local, int nsteps, int new_cycle, hf2d_step_report* report);
+int  hf2d_slab_read_node(hf2d_slab* const* local, int n_local, int i_global, int j, double* p, double* Tg);
+
 #ifdef __cplusplus
 }
 #endif

@@ -66,7 +66,9 @@ EXPORTS = ["hf2d_gpu_last_error", "hf2d_gpu_device_count", "hf2d_gpu_create", "h
            "hf2d_gpu_set_stream", "hf2d_gpu_set_timing", "hf2d_gpu_get_timing", "hf2d_gpu_dt_export", "hf2d_gpu_dt_import", "hf2d_gpu_launch_count",
            "hf2d_gpu_step_part", "hf2d_gpu_lane_fork", "hf2d_gpu_lane_join", "hf2d_gpu_side_stream", "hf2d_gpu_halo_pack_lane",
            "hf2d_gpu_halo_unpack_lane", "hf2d_gpu_edge_tile_counts", "hf2d_gpu_set_min_distance_to_wall", "hf2d_gpu_set_global_time", "hf2d_gpu_recalc_y_plus", "hf2d_gpu_residual_sums", "hf2d_gpu_set_min_distance_to_wall_slab", "hf2d_gpu_keep_gradients",
-           "hf2d_gpu_wall_distance_noalloc"]
+           "hf2d_gpu_wall_distance_noalloc", "hf2d_slab_cuts", "hf2d_slab_create", "hf2d_slab_destroy", "hf2d_slab_solver", "hf2d_slab_columns",
+           "hf2d_slab_ipc_handle_bytes", "hf2d_slab_ipc_handle", "hf2d_slab_connect_ipc", "hf2d_slab_connect_local", "hf2d_slab_upload",
+           "hf2d_slab_download", "hf2d_slab_upload_local", "hf2d_slab_download_local", "hf2d_slab_run", "hf2d_slab_read_node"]
 
 
 def lib():
@@ -123,6 +125,19 @@ def lib():
         L.hf2d_gpu_launch_count.restype = C.c_ulonglong
         L.hf2d_gpu_keep_gradients.argtypes = [C.c_void_p, C.c_int]
         L.hf2d_gpu_wall_distance_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.hf2d_slab_cuts.argtypes = [C.c_void_p, C.POINTER(NodeLayout), C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        L.hf2d_slab_create.argtypes = [C.POINTER(Cfg), C.c_int, C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]
+        L.hf2d_slab_destroy.argtypes = [C.c_void_p]
+        L.hf2d_slab_solver.argtypes = [C.c_void_p]; L.hf2d_slab_solver.restype = C.c_void_p
+        L.hf2d_slab_columns.argtypes = [C.c_void_p] + [C.POINTER(C.c_int)] * 4
+        L.hf2d_slab_ipc_handle_bytes.restype = C.c_size_t
+        L.hf2d_slab_ipc_handle.argtypes = [C.c_void_p, C.c_void_p]
+        L.hf2d_slab_connect_ipc.argtypes = [C.c_void_p, C.c_void_p]
+        L.hf2d_slab_connect_local.argtypes = [C.c_void_p, C.c_int]
+        for f in (L.hf2d_slab_upload, L.hf2d_slab_download, L.hf2d_slab_upload_local, L.hf2d_slab_download_local):
+            f.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(NodeLayout), C.c_int]
+        L.hf2d_slab_run.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(StepReport)]
+        L.hf2d_slab_read_node.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
         _lib = L
     return _lib
 
@@ -360,3 +375,89 @@ class Solver:
         _ck(lib().hf2d_gpu_set_min_distance_to_wall(self._h, walls.ctypes.data, len(walls), float(x0), l_min.ctypes.data,
                                                     i_wall.ctypes.data, j_wall.ctypes.data, status.ctypes.data))
         return l_min, i_wall, j_wall, status
+
+
+def slab_cuts(J, layout: dict, world: int, min_cols: int = 2):
+    """hf2d_slab_cuts: X-slab boundaries of the host image J (nx, ny records) with equal numbers of active nodes."""
+    nx, ny = J.shape
+    cuts = (C.c_int * (world + 1))()
+    lay = make_layout(layout)
+    _ck(lib().hf2d_slab_cuts(J.ctypes.data, C.byref(lay), nx, ny, world, min_cols, cuts))
+    return list(cuts)
+
+
+class _BorrowedSolver(Solver):
+    """The hf2d_gpu handle inside a slab: same calls as Solver, owned (and destroyed) by the slab."""
+
+    def __init__(self, handle, cfg, layout, nx, ny):
+        self._h = C.c_void_p(handle)
+        self.cfg, self.layout, self.nx, self.ny = cfg, layout, nx, ny
+
+    def close(self):
+        self._h = C.c_void_p()
+
+
+class Slab:
+    """One rank of the C X-slab driver (csrc/hf2d_slab.inc): ghost columns by direct stores into the neighbour's HBM."""
+
+    def __init__(self, cfg_global: dict, layout: dict, device: int, rank: int, world: int, cuts, **kw):
+        self._s = C.c_void_p()
+        self.layout = make_layout(layout)
+        c, self._keep = make_cfg(cfg_global, **kw)
+        self.rank, self.world, self.device = rank, world, device
+        arr = (C.c_int * (world + 1))(*[int(v) for v in cuts])
+        _ck(lib().hf2d_slab_create(C.byref(c), device, rank, world, arr, C.byref(self._s)))
+        v = [C.c_int() for _ in range(4)]
+        _ck(lib().hf2d_slab_columns(self._s, *[C.byref(x) for x in v]))
+        self.c0, self.c1, self.gl, self.gr = (x.value for x in v)
+        self.solver = _BorrowedSolver(lib().hf2d_slab_solver(self._s), cfg_global, self.layout, self.c1 - self.c0 + self.gl + self.gr, c.ny)
+
+    def close(self):
+        if self._s:
+            self.solver.close()
+            lib().hf2d_slab_destroy(self._s)
+            self._s = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def ipc_handle(self) -> bytes:
+        n = lib().hf2d_slab_ipc_handle_bytes()
+        buf = C.create_string_buffer(n)
+        _ck(lib().hf2d_slab_ipc_handle(self._s, buf))
+        return buf.raw
+
+    def connect_ipc(self, handles: bytes):
+        assert len(handles) == self.world * lib().hf2d_slab_ipc_handle_bytes()
+        _ck(lib().hf2d_slab_connect_ipc(self._s, handles))
+
+    @staticmethod
+    def connect_local(slabs):
+        arr = (C.c_void_p * len(slabs))(*[s._s for s in slabs])
+        _ck(lib().hf2d_slab_connect_local(arr, len(slabs)))
+
+    def upload(self, J_global, pinned=False):
+        _ck(lib().hf2d_slab_upload(self._s, Solver._ptr(J_global), C.byref(self.layout), int(pinned)))
+
+    def download(self, J_global, pinned=False):
+        _ck(lib().hf2d_slab_download(self._s, Solver._ptr(J_global), C.byref(self.layout), int(pinned)))
+
+    def upload_local(self, J_slab, pinned=False):
+        _ck(lib().hf2d_slab_upload_local(self._s, Solver._ptr(J_slab), C.byref(self.layout), int(pinned)))
+
+    def download_local(self, J_slab, pinned=False):
+        _ck(lib().hf2d_slab_download_local(self._s, Solver._ptr(J_slab), C.byref(self.layout), int(pinned)))
+
+    @staticmethod
+    def run_all(slabs, nsteps: int, new_cycle: bool = True) -> StepReport:
+        """hf2d_slab_run on the slabs this process drives (all ranks in one process, or [mine])."""
+        arr = (C.c_void_p * len(slabs))(*[s._s for s in slabs])
+        rep = StepReport()
+        _ck(lib().hf2d_slab_run(arr, len(slabs), nsteps, int(new_cycle), C.byref(rep)))
+        return rep
+
+    def run(self, nsteps: int, new_cycle: bool = True) -> StepReport:
+        return Slab.run_all([self], nsteps, new_cycle)

@@ -338,3 +338,121 @@ class SlabRunner(SlabProtocol):
 
     def close(self):
         self.solver.close()
+
+
+class CSlabRunner:
+    """bench.py's driver for N > 1: one process per GPU, stepping through the C X-slab driver (csrc/hf2d_slab.inc) --
+    ghost columns, dt and residual accumulators travel by direct stores into the neighbours' HBM over NVLink (cudaIpc
+    peer memory + flag words); torch.distributed only carries the 64-byte mailbox handles once, the timing max and the
+    barriers.  Same interface as SlabRunner (the torch.distributed/NCCL protocol harness)."""
+
+    def __init__(self, nx, ny, model="keps", rank=0, world=1, device=0, rms_every=None, J=None, cfg=None, lay=None, cuts=None):
+        import torch
+        self.torch, self.rank, self.world, self.device = torch, rank, world, device
+        if cuts is None:
+            cuts = [r * nx for r in range(world + 1)]
+        self.gl = 1 if (world > 1 and rank > 0) else 0
+        self.gr = 1 if (world > 1 and rank < world - 1) else 0
+        if J is None:
+            w = cuts[rank + 1] - cuts[rank]
+            J, cfg, lay = gridgen.three_cylinders(w + self.gl + self.gr, ny, model=model, i0=cuts[rank] - self.gl, nx_total=cuts[-1])
+        self.J, self.cfg, self.layout = J, cfg, lay
+        self.slab = cabi.Slab(cfg, lay, device, rank, world, cuts, rms_every=rms_every)
+        self.solver = self.slab.solver
+        if world > 1:
+            dist = torch.distributed
+            n = len(self.slab.ipc_handle())
+            mine = torch.tensor(list(self.slab.ipc_handle()), dtype=torch.uint8, device=torch.device("cuda", device))
+            allh = [torch.empty(n, dtype=torch.uint8, device=mine.device) for _ in range(world)]
+            dist.all_gather(allh, mine)
+            self.slab.connect_ipc(b"".join(bytes(t.cpu().tolist()) for t in allh))
+        self.slab.upload_local(J)
+        self.launches_last = 0
+
+    def barrier(self):
+        self.torch.cuda.synchronize()
+        if self.world > 1:
+            self.torch.distributed.barrier()
+            self.torch.cuda.synchronize()
+
+    def allreduce_sum(self, v):
+        if self.world == 1:
+            return int(v)
+        t = self.torch.tensor([int(v)], dtype=self.torch.int64, device=self.torch.device("cuda", self.device))
+        self.torch.distributed.all_reduce(t)
+        return int(t.item())
+
+    def step(self, n, new_cycle=True):
+        rep = self.slab.run(n, new_cycle)
+        self.launches_last = rep.kernel_launches
+        return rep
+
+    def timed_steps(self, k):
+        """Device time of k steps in ms (CUDA events on the slab's own stream around the enqueued steps), max over ranks."""
+        torch = self.torch
+        self.barrier()
+        rep = self.step(k)
+        ms = rep.gpu_ms
+        if self.world > 1:
+            t = torch.tensor([ms], dtype=torch.float64, device=torch.device("cuda", self.device))
+            torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    def active_cells(self):
+        own = self.J[self.gl:self.J.shape[0] - self.gr]
+        ct = own["CT"]
+        act = int((((ct & 0x40000000) == 0) & ((ct & 0x8000001f) != 0x8000001f) & ((ct & 0x80000000) != 0)).sum())
+        return act, own.size
+
+    def e2e_cycles(self, nsteps, cycles=3):
+        """`cycles` output cycles through HOST memory (pinned): upload AoS + nsteps + download AoS each, wall clock around
+        the calls bracketed by barriers; per cycle the max over ranks; returns the list of seconds."""
+        import time
+        torch = self.torch
+        host = torch.empty(self.J.nbytes, dtype=torch.uint8, pin_memory=True)
+        Jp = host.numpy().view(self.J.dtype).reshape(self.J.shape)
+        out = []
+        for _ in range(max(1, cycles)):
+            Jp[...] = self.J                   # every cycle starts from the same grid image (outside the timed region)
+            self.barrier()
+            t0 = time.perf_counter()
+            self.slab.upload_local(Jp, pinned=True)
+            self.slab.run(nsteps)
+            self.slab.download_local(Jp, pinned=True)
+            torch.cuda.synchronize()
+            el = time.perf_counter() - t0
+            if self.world > 1:
+                t = torch.tensor([el], dtype=torch.float64, device=torch.device("cuda", self.device))
+                torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+                el = float(t.item())
+            out.append(el)
+        return out
+
+    def close(self):
+        self.barrier()          # nobody frees its mailbox while a neighbour may still write into it
+        self.slab.close()
+
+
+def slab_parity_check(rank, world, device, model="keps", nx=192, ny=160, nsteps=7):
+    """Run on the box before timing (bench.py, N > 1): a small grid stepped by the C slab driver on all `world` GPUs against
+    the single-domain run of the same grid on this rank's own GPU; True iff this rank's owned columns agree BIT FOR BIT in
+    every field the step owns.  The caller all-reduces the verdicts."""
+    J, cfg, lay = gridgen.three_cylinders(nx, ny, model=model)
+    cuts = cabi.slab_cuts(J, lay, world)
+    s = cabi.Solver(cfg, lay, device=device)
+    ref = np.array(J, copy=True)
+    s.upload_aos(ref); s.step(nsteps); s.download_aos(ref); s.close()
+    lo, hi = cuts[rank] - (1 if rank > 0 else 0), cuts[rank + 1] + (1 if rank < world - 1 else 0)
+    r = CSlabRunner(nx, ny, model=model, rank=rank, world=world, device=device, J=J[lo:hi].copy(), cfg=cfg, lay=lay, cuts=cuts)
+    r.step(nsteps)
+    got = np.array(r.J, copy=True)
+    r.slab.download_local(got)
+    own = got[r.gl:got.shape[0] - r.gr]
+    want = ref[cuts[rank]:cuts[rank + 1]]
+    ok = True
+    for f in ("S", "beta", "A", "B", "U", "V", "Tg", "p", "k", "R", "CP", "lam", "mu", "mu_t"):
+        a, b = np.asarray(own[f]), np.asarray(want[f])
+        ok = ok and bool(((a == b) | ((a != a) & (b != b))).all())
+    r.close()
+    return ok

@@ -34,6 +34,45 @@ extern char RMSFileName[255], MonitorsFileName[255], ErrFileName[255], TecPlotFi
 extern ofstream *pRMS_OutFile, *pMonitors_OutFile, *pHeatFlux_OutFile;
 extern UArray<Flow2D*>* Flow2DList;
 
+// ---- one GPU or N: the same five verbs ----
+// HF2D_GPUS=N (N > 1): the grid is cut into N X-slabs with equal numbers of active nodes (hf2d_slab_cuts, the rule of
+// ScanArea, deeps2d_core.cpp:2153, 2207-2216), one slab per GPU (devices r mod the number of GPUs present), all driven from
+// this one host thread -- what hf2d_start.cpp:149-175 + the per-rank DEEPS2D_Run(o_stream, pJ, pC, rank, last_rank, x0) of
+// the MPI build (deeps2d_core.hpp:206-212, hf2d_start.cpp:285) do with one process per sub-domain.  Every slab reads its
+// columns from J and writes its owned columns back into J, so the per-cycle writers below see one grid.
+static hf2d_gpu* g_h = NULL;
+static hf2d_slab* g_slab[64];
+static int g_nslab = 0;
+static int eng_upload(const hf2d_node_layout* lay, int pinned) {
+    if (!g_nslab) return hf2d_gpu_upload_aos(g_h, J->GetMatrixPtr(), lay, pinned);
+    for (int r = 0; r < g_nslab; r++) { const int rc = hf2d_slab_upload(g_slab[r], J->GetMatrixPtr(), lay, pinned); if (rc) return rc; }
+    return 0;
+}
+static int eng_download(const hf2d_node_layout* lay, int pinned) {
+    if (!g_nslab) return hf2d_gpu_download_aos(g_h, J->GetMatrixPtr(), lay, pinned);
+    for (int r = 0; r < g_nslab; r++) { const int rc = hf2d_slab_download(g_slab[r], J->GetMatrixPtr(), lay, pinned); if (rc) return rc; }
+    return 0;
+}
+static int eng_step(int first_of_cycle, int n, hf2d_step_report* rep) {
+    if (!g_nslab) return first_of_cycle ? hf2d_gpu_step(g_h, n, rep) : hf2d_gpu_step_continue(g_h, n, rep);
+    return hf2d_slab_run(g_slab, g_nslab, n, first_of_cycle, rep);
+}
+static void eng_keep_gradients(int on) {
+    if (!g_nslab) { hf2d_gpu_keep_gradients(g_h, on); return; }
+    for (int r = 0; r < g_nslab; r++) hf2d_gpu_keep_gradients(hf2d_slab_solver(g_slab[r]), on);
+}
+static void eng_read_node(int i, int j, double* p, double* T) {
+    if (!g_nslab) hf2d_gpu_read_node(g_h, i, j, p, T); else hf2d_slab_read_node(g_slab, g_nslab, i, j, p, T);
+}
+static void eng_set_global_time(double t) {
+    if (!g_nslab) { hf2d_gpu_set_global_time(g_h, t); return; }
+    for (int r = 0; r < g_nslab; r++) hf2d_gpu_set_global_time(hf2d_slab_solver(g_slab[r]), t);
+}
+static void eng_destroy() {
+    if (!g_nslab) { hf2d_gpu_destroy(g_h); return; }
+    for (int r = 0; r < g_nslab; r++) hf2d_slab_destroy(g_slab[r]);
+}
+
 static void die(ofstream* f, const char* what) {
     *f << "\nhf2d_gpu: " << what << ": " << hf2d_gpu_last_error() << "\n" << flush;
     Abort_OpenHyperFLOW2D();
@@ -108,13 +147,30 @@ void DEEPS2D_Run(ofstream* f_stream) {
     const hf2d_node_layout lay = node_layout();
     hf2d_gpu* h = NULL;
     const char* dev = getenv("HF2D_DEVICE");
-    if (hf2d_gpu_create(&cfg, dev ? atoi(dev) : 0, &h)) die(f_stream, "create");
+    const int n_gpus = getenv("HF2D_GPUS") ? atoi(getenv("HF2D_GPUS")) : 1;
+    if (n_gpus > 1) {
+        if (n_gpus > 64) die(f_stream, "HF2D_GPUS > 64");
+        const int n_dev = hf2d_gpu_device_count();
+        if (n_dev < 1) die(f_stream, "no CUDA device");
+        int cuts[65];
+        if (hf2d_slab_cuts(J->GetMatrixPtr(), &lay, (int)MaxX, (int)MaxY, n_gpus, 2, cuts)) die(f_stream, "slab cuts");
+        for (int r = 0; r < n_gpus; r++)
+            if (hf2d_slab_create(&cfg, (r + (dev ? atoi(dev) : 0)) % n_dev, r, n_gpus, cuts, &g_slab[r])) die(f_stream, "slab create");
+        g_nslab = n_gpus;
+        if (hf2d_slab_connect_local(g_slab, g_nslab)) die(f_stream, "slab connect");
+        *f_stream << "hf2d_gpu: " << n_gpus << " X-slabs on " << (n_gpus < n_dev ? n_gpus : n_dev) << " GPU(s), cuts at columns";
+        for (int r = 0; r <= n_gpus; r++) *f_stream << " " << cuts[r];
+        *f_stream << "\n" << flush;
+    } else {
+        if (hf2d_gpu_create(&cfg, dev ? atoi(dev) : 0, &h)) die(f_stream, "create");
+        g_h = h;
+    }
     // J lives as long as the run: page-lock it once so every per-cycle download runs at PCIe speed (optional)
     const int pinned = hf2d_gpu_pin_host(J->GetMatrixPtr(), (size_t)J->GetMatrixSize()) == 0;
     // Optional second seam (INTEGRATION.md, HF2D_GPU_WALL_DISTANCE=1): SetMinDistanceToWall2D on the GPU.  main() has
     // already run the host version by the time DEEPS2D_Run is called (hf2d_start.cpp:298) -- a maintainer would drop that
     // call -- so its results are wiped from J first: what the step and the swap file see is what the GPU computed.
-    const bool gpu_wall_distance = getenv("HF2D_GPU_WALL_DISTANCE") && atoi(getenv("HF2D_GPU_WALL_DISTANCE")) &&
+    const bool gpu_wall_distance = n_gpus <= 1 && getenv("HF2D_GPU_WALL_DISTANCE") && atoi(getenv("HF2D_GPU_WALL_DISTANCE")) &&
                                    ProblemType == SM_NS && WallNodes && WallNodes->GetNumElements() > 0;   // (no walls: the host's i_wall = j_wall = 0 stand)
     if (gpu_wall_distance) {
         for (int i = 0; i < MaxX; i++) for (int j = 0; j < MaxY; j++) {
@@ -122,7 +178,7 @@ void DEEPS2D_Run(ofstream* f_stream) {
             if (nd.isCond2D(CT_NODE_IS_SET_2D) && !nd.isCond2D(CT_SOLID_2D)) { nd.l_min = -1.; nd.i_wall = -1; nd.j_wall = -1; }
         }
     }
-    if (hf2d_gpu_upload_aos(h, J->GetMatrixPtr(), &lay, pinned)) die(f_stream, "upload");
+    if (eng_upload(&lay, pinned)) die(f_stream, "upload");
     if (gpu_wall_distance) {
         const size_t N = (size_t)MaxX * MaxY;
         double* wl = new double[N]; int* wi = new int[N]; int* wj = new int[N]; unsigned char* ws = new unsigned char[N];
@@ -179,9 +235,10 @@ void DEEPS2D_Run(ofstream* f_stream) {
             // the step with in-cycle index `done` is an output step iff done % NOutStep == 0: run up to and including it
             int n = (done % NOutStep == 0) ? 1 : (NOutStep - done % NOutStep);
             if (done + n > Nstep) n = Nstep - done;
-            const int rc = done == 0 ? hf2d_gpu_step(h, n, &rep) : hf2d_gpu_step_continue(h, n, &rep);
+            eng_keep_gradients(done + n >= Nstep);      // the records' gradient members are observable after the cycle's last step only
+            const int rc = eng_step(done == 0, n, &rep);
             if (rc == HF2D_EUNSTABLE) {               // Tg < 0 (deeps2d_core.cpp:1246-1316): error snapshot + abort
-                hf2d_gpu_download_aos(h, J->GetMatrixPtr(), &lay, pinned);
+                eng_download(&lay, pinned);
                 *f_stream << "\nTg=" << J->GetValue(rep.err_i, rep.err_j).Tg << " K. p=" << J->GetValue(rep.err_i, rep.err_j).p
                           << " Pa dt=" << rep.dt << " sec.\nComputational unstability in node (" << rep.err_i << "," << rep.err_j << ") on iteration "
                           << rep.iter << "\n" << flush;
@@ -199,7 +256,7 @@ void DEEPS2D_Run(ofstream* f_stream) {
                     for (int m = 0; m < (int)MonitorPointsArray->GetNumElements(); m++) {
                         MonitorPoint& mp = MonitorPointsArray->GetElement(m);
                         double pp = 0., tt = 0.;
-                        hf2d_gpu_read_node(h, (int)(mp.MonitorXY.GetX() / dx), (int)(mp.MonitorXY.GetY() / dy), &pp, &tt);
+                        eng_read_node((int)(mp.MonitorXY.GetX() / dx), (int)(mp.MonitorXY.GetY() / dy), &pp, &tt);
                         mp.p = pp; mp.T = tt;
                     }
                 }
@@ -228,8 +285,8 @@ void DEEPS2D_Run(ofstream* f_stream) {
             }
         }
         // --- cycle end (deeps2d_core.cpp:1762-1849): grid back to the host image, then the reference's own writers ---
-        hf2d_gpu_set_global_time(h, GlobalTime);            // FlowNode2D::time of the swept nodes (:867): still the cycle's start value
-        if (hf2d_gpu_download_aos(h, J->GetMatrixPtr(), &lay, pinned)) die(f_stream, "download");
+        eng_set_global_time(GlobalTime);                    // FlowNode2D::time of the swept nodes (:867): still the cycle's start value
+        if (eng_download(&lay, pinned)) die(f_stream, "download");
         if (XCutArray->GetNumElements() > 0) {
             for (int i_xcut = 0; i_xcut < (int)XCutArray->GetNumElements(); i_xcut++) {
                 XCut* c = XCutArray->GetElementPtr(i_xcut);
@@ -286,7 +343,7 @@ void DEEPS2D_Run(ofstream* f_stream) {
     } while (MonitorCondition);
     DataSnapshot(OutFileName, WM_REWRITE);
     if (pinned) hf2d_gpu_unpin_host(J->GetMatrixPtr());
-    hf2d_gpu_destroy(h);
+    eng_destroy();
     *f_stream << "\nReady. Computation finished.\n" << flush;
     Exit_OpenHyperFLOW2D();
 }

@@ -3,6 +3,11 @@ import sys
 
 import pytest
 
+# several X-slab ranks on ONE GPU (the slab-driver tests on a 1-GPU box) use up to 12 streams whose kernels wait for each
+# other: every stream needs a hardware queue of its own (default 8), or a waiting kernel could sit in front of the one it
+# waits for.  Must be set before the CUDA context exists.
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 for p in (ROOT, os.path.join(ROOT, "oracle")):
     if p not in sys.path:

@@ -40,12 +40,13 @@ def _deck(case, nmax, nout, exit_time):
     return text.replace("<data/ExitMonitorValue=1.e-30>", f"<data/ExitMonitorValue={exit_time!r}>")
 
 
-def _run(binary, deck, case, wd):
+def _run(binary, deck, case, wd, env=None):
     os.makedirs(wd)
     with open(os.path.join(wd, case + ".dat"), "w") as f:
         f.write(deck)
     with open(os.path.join(wd, "log.txt"), "w") as log:
-        rc = subprocess.run([binary, case + ".dat"], cwd=wd, stdout=log, stderr=subprocess.STDOUT, timeout=600).returncode
+        rc = subprocess.run([binary, case + ".dat"], cwd=wd, stdout=log, stderr=subprocess.STDOUT, timeout=600,
+                            env=dict(os.environ, **(env or {}))).returncode
     out = open(os.path.join(wd, "log.txt")).read()
     assert rc == 0, out[-3000:]
     nx = int([l for l in deck.splitlines() if l.startswith("<data/MaxX=")][0].split("=")[1][:-1])
@@ -91,3 +92,32 @@ def test_reference_program_with_gpu_time_loop(case, nmax, nout, exit_time, exact
         else:
             scale = max(float(np.abs(b).max()), 1e-300)
             assert float(np.abs(a - b).max()) / scale <= 1e-10, f
+
+
+
+@pytest.mark.skipif(not (os.path.exists(REF) and os.path.exists(GPU)), reason="oracle/_ref not built (make -C oracle ref)")
+@pytest.mark.parametrize("n_gpus", [2, 4])
+@pytest.mark.parametrize("case,nmax,nout,exit_time,exact", [CASES[2], CASES[3]])
+def test_reference_program_on_several_gpus(case, nmax, nout, exit_time, exact, n_gpus, tmp_path):
+    """HF2D_GPUS=N: the reference program's grid cut into N X-slabs by active-node count and stepped by the C slab driver
+    (csrc/hf2d_slab.inc; ghost columns stored straight into the neighbour's HBM).  The swap file it leaves is the single-GPU
+    program's BIT FOR BIT (exact seams), hence the unmodified program's within the usual bound.  With fewer than N GPUs on
+    the box the slabs share devices (r mod the number present): same kernels, flags and schedule."""
+    deck = _deck(case, nmax, nout, exit_time)
+    Jr, rms_r, _ = _run(REF, deck, case, str(tmp_path / "ref"))
+    J1, rms_1, _ = _run(GPU, deck, case, str(tmp_path / "gpu1"))
+    Jn, rms_n, out = _run(GPU, deck, case, str(tmp_path / "gpun"), env={"HF2D_GPUS": str(n_gpus), "CUDA_DEVICE_MAX_CONNECTIONS": "32"})
+    assert f"hf2d_gpu: {n_gpus} X-slabs" in out
+    assert len(rms_n) == len(rms_r) == len(rms_1)
+    for a, b in zip(rms_n, rms_r):
+        assert np.allclose(a, b, rtol=2e-5, atol=1e-300), (a, b)
+    for f in Jn.dtype.names:            # every member of every record, not only the step's
+        a, b = Jn[f], J1[f]
+        same = (a == b) | ((a != a) & (b != b)) if a.dtype.kind == "f" else (a == b)
+        assert same.all(), f"{case} x{n_gpus}: member {f} differs from the single-GPU program in {int((~same).sum())} entries"
+    for f in FIELDS:
+        a, b = Jn[f], Jr[f]
+        if exact or a.dtype.kind in "iu":
+            assert ((a == b) | ((a != a) & (b != b))).all(), f
+        else:
+            assert float(np.abs(a - b).max()) / max(float(np.abs(b).max()), 1e-300) <= 1e-10, f
