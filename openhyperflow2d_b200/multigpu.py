@@ -356,6 +356,7 @@ class CSlabRunner:
         if J is None:
             w = cuts[rank + 1] - cuts[rank]
             J, cfg, lay = gridgen.three_cylinders(w + self.gl + self.gr, ny, model=model, i0=cuts[rank] - self.gl, nx_total=cuts[-1])
+            cfg = dict(cfg, MaxX=cuts[-1])       # the slab driver is given the UNDIVIDED grid's configuration
         self.J, self.cfg, self.layout = J, cfg, lay
         self.slab = cabi.Slab(cfg, lay, device, rank, world, cuts, rms_every=rms_every)
         self.solver = self.slab.solver
