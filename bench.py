@@ -34,6 +34,9 @@ for p in (ROOT, os.path.join(ROOT, "oracle")):
 METRIC = "fp64_active_cell_updates_per_s"
 UNIT = "cell-updates/s"
 NX_PER_GPU, NY = 2048, 4096
+REF_NX, REF_NY = 1024, 512          # grid of the reference (CPU) arm, see reference_arm()
+WORKLOAD = ("BASELINE configs[3]: hypersonic flow around three cylinders, NS k-eps URANS (9 equations; k-eps in place of SST: the reference "
+            "has no SST arithmetic, hyper_flow_node.hpp:919-926), flat")
 
 
 def peaks():
@@ -175,8 +178,12 @@ def reference_arm(args):
     if rank != 0:
         return
     nthreads = os.cpu_count() or 1
-    nx, ny = 512, 256
-    nsteps = int(min(max(4 * (args.warmup + args.steps), 100), 400))
+    # Grid of the reference arm: the reference's own START-UP (SetMinDistanceToWall2D, an O(nodes x wall nodes) host loop,
+    # deeps2d_core.cpp:4783-4832) takes ~40 s at 1024x512 and would take the better part of an hour at the GPU arm's
+    # 2048x4096, so the same deck is timed on the largest grid whose start-up fits a bench run; cell-updates/s of the CPU
+    # solver does not depend on the grid size (2.4-2.9 M at 512x256, 1024x512 and 1024x1024).
+    nx, ny = REF_NX, REF_NY
+    nsteps = int(min(max(4 * (args.warmup + args.steps), 100), 200))
     r = run_reference_binary("ohf_omp", nx, ny, nsteps, nthreads)
     if r is not None:
         ser = run_reference_binary("ohf_serial", nx, ny, min(nsteps, 100), 1)
@@ -189,7 +196,8 @@ def reference_arm(args):
         v, kind, cores, how, ms = cb["value"], "port", 1, cb["sample"] + " (oracle/_ref not present: oracle port used)", None
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"BASELINE configs[3]: three cylinders, NS k-eps URANS (9 equations), flat; bounded sample {nx}x{ny}, {nsteps} steps"},
+            "config": {"workload": WORKLOAD, "grid": f"{nx}x{ny}", "sample": f"one run of {nsteps} steps",
+                       "grid_note": "the reference's O(nodes x walls) start-up limits the CPU arm's grid; the GPU arm runs 2048x4096 per GPU"},
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": how},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
@@ -215,12 +223,98 @@ def cpu_baseline(model):
     """CPU baseline beside the GPU number: the UNMODIFIED reference (oracle/_ref/ohf_serial, one core -- its OpenMP
     build does not scale) on a bounded sample; the oracle port when the reference binary is absent."""
     if model == "keps":
-        r = run_reference_binary("ohf_serial", 512, 256, 60, 1)
+        r = run_reference_binary("ohf_serial", 512, 256, 60, 1)       # (one core: a quarter of the reference arm's grid keeps the default run short)
         if r is not None:
             return {"value": r[0], "unit": UNIT, "cores": 1, "kind": "reference",
                     "sample": f"unmodified reference, serial build (oracle/_ref/ohf_serial), three-cylinder k-eps deck 512x256 "
                               f"({r[1]} active cells), 60 steps, the solver's own 'average speed' line ({r[2]:.3g} step/s)"}
     return cpu_baseline_port(model)
+
+
+# ---- the other BASELINE configs: grids drawn by the reference's OWN deck parser and rasterisers -------------------------------
+# oracle/_ref/ohf_dump is the unmodified reference + a hook that writes the grid image and the step's scalars right before
+# the first step (oracle/ref_hook.cpp); it travels to the GPU box with the snapshot.  Decks come from the fixtures' generator
+# (tests/golden/make_golden.py), scaled up by `scale` with the geometry kept (dx = 1e-3 / scale).  Sizes are what the
+# reference's start-up allows in a bench run (its wall-distance pass is O(nodes x walls)); each line states its own grid.
+def _deck_cases():
+    sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+    import make_golden as G
+    C, GEO, R2 = G.cases(), G.geometry_cases(), G.r2_cases()
+    return G, {
+        # name: (BASELINE config, deck spec, base nx, base ny, scale, what differs from the named config)
+        "c1": ("configs[0]: supersonic duct with narrowing, flat, inviscid, single component", C["euler_duct"]["deck"], 60, 40, 7, "420x280 (named ~400x100)"),
+        "c2": ("configs[1]: shock reflection over a ramp in a duct, flat, viscous laminar", C["ns_laminar"]["deck"], 60, 40, 34, "2040x1360 (named ~2k x 500)"),
+        "c3": ("configs[2]: NACA airfoil, flat, k-eps RANS in place of SST (no SST arithmetic in the reference)", GEO["airfoil_keps"]["deck"], 96, 64, 16,
+               "1536x1024 (named ~4k x 2k: the reference's O(nodes x walls) start-up does not fit a bench run there)"),
+        "c5": ("configs[4]: axisymmetric hydrogen jets burning in hot oxidiser, multicomponent reacting, k-eps in place of SST", R2["plain_axi_burn_keps"]["deck"], 40, 100, 40,
+               "1600x4000 (named ~8k x 2k)"),
+    }
+
+
+def config_grid(name):
+    """(J, cfg, layout, label) of BASELINE config `name`, drawn by the reference program itself."""
+    import numpy as np
+    from openhyperflow2d_b200 import aos, config
+    G, T = _deck_cases()
+    label, spec, bx, by, sc, note = T[name]
+    nx, ny = bx * sc, by * sc
+    spec = dict(spec, nx=nx, ny=ny, dx=1e-3 / sc, dy=1e-3 / sc, nmax=1)
+    spec["delta_bl"] = spec.get("delta_bl", 1e-3)
+    # area seeds are node indices: keep them where they were in physical space
+    spec["areas"] = [dict(a, seed=(min(a["seed"][0] * sc, nx - 4) if a["seed"][0] < bx - 8 else nx - 4 * sc, a["seed"][1] * sc)) for a in spec["areas"]]
+    exe = os.path.join(ROOT, "oracle", "_ref", "ohf_dump")
+    if not os.path.exists(exe):
+        raise SystemExit("bench.py --config needs oracle/_ref/ohf_dump (built by __graft_entry__.build() where the reference tree is present)")
+    wd = tempfile.mkdtemp(prefix="ohf_cfg_")
+    with open(os.path.join(wd, "cfg.dat"), "w") as f:
+        f.write(G.make_deck("cfg", **spec))
+    env = dict(os.environ, OHF_DUMP_DIR=wd, OHF_EXIT_TIME="1e-300", OHF_NSTEP="1", OHF_DUMP_ONLY="1")
+    t0 = time.time()
+    with open(os.path.join(wd, "log.txt"), "w") as log:
+        subprocess.run([exe, "cfg.dat"], cwd=wd, env=env, stdout=log, stderr=subprocess.STDOUT, timeout=1500)
+    if not os.path.exists(os.path.join(wd, "state0.hf2d")):
+        raise SystemExit("ohf_dump left no grid image:\n" + open(os.path.join(wd, "log.txt")).read()[-2000:])
+    lay = aos.parse_layout(os.path.join(wd, "layout.txt"))
+    cfg = config.parse_cfg(os.path.join(wd, "cfg.txt"))
+    J = np.fromfile(os.path.join(wd, "state0.hf2d"), dtype=aos.ref_dtype(lay)).reshape(nx, ny)
+    for fn in os.listdir(wd):
+        os.remove(os.path.join(wd, fn))
+    return J, cfg, lay, f"BASELINE {label}; grid {note}; drawn by the reference's own deck parser and rasterisers in {time.time() - t0:.0f} s"
+
+
+def run_config(args):
+    """One JSON line for one of the other BASELINE configs on ONE GPU: device-timed steps on the reference-drawn grid."""
+    import numpy as np
+    import torch
+    from openhyperflow2d_b200 import cabi
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- this framework has no CPU fallback")
+    J, cfg, lay, label = config_grid(args.config)
+    cfg["NOutStep"] = args.rms_every
+    s = cabi.Solver(cfg, lay, device=0, rms_every=args.rms_every)
+    s.upload_aos(J)
+    act = s.active_cells()[0]
+    W, K = max(args.warmup, 3), args.steps
+    s.step(W)
+    s.set_timing(True)
+    with ClockSampler(0) as cs:
+        rep = s.step_continue(K)
+    kt = s.get_timing()
+    n_plain, n_gen, tc, tr = s.tile_counts()
+    bpc = s.bytes_per_cell()
+    peak, peak_src = peaks()
+    ms = rep.gpu_ms
+    gbs = bpc * act * K / (ms * 1e-3) / 1e9
+    line = {"metric": METRIC, "value": act * K / (ms * 1e-3), "unit": UNIT, "n_gpus": 1, "steps": K, "warmup": W, "ms_per_step": ms / K,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": label, "grid": f"{J.shape[0]}x{J.shape[1]}", "active_cells": act, "ProblemType": cfg["ProblemType"], "FT": cfg["FT"],
+                       "TurbExtModel": cfg["TurbExtModel"], "tiles": {"plain": n_plain, "general": n_gen, "cols": tc, "rows": tr}, "rms_every": args.rms_every},
+            "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak, "traffic": None, "peak_source": peak_src,
+                         "kernel": "whole step (algorithmic bytes per active cell, DESIGN.md)", "bytes_per_active_cell": bpc,
+                         "plain_kernels_ms": {"k1a": kt["k1a_plain_ms"], "k1b": kt["k1b_plain_ms"], "k2": kt["k2_plain_ms"]}},
+            "gpu_launches": int(rep.kernel_launches), "clocks": cs.summary(), "dt": rep.dt}
+    s.close()
+    print(json.dumps(line))
 
 
 def main():
@@ -238,6 +332,8 @@ def main():
     ap.add_argument("--rms-every", type=int, default=100, help="NOutStep: residual norms reduced every n-th step and on the last one")
     ap.add_argument("--e2e-steps", type=int, default=500,
                     help="steps per output cycle (Nmax) of the end-to-end leg; the reference's own decks use 500 (TriplePoint.dat) to 24000 (Step.dat)")
+    ap.add_argument("--config", default=None, choices=["c1", "c2", "c3", "c5"],
+                    help="one of the other BASELINE configs on one GPU, grid drawn by the reference program (oracle/_ref/ohf_dump); default: configs[3] (c4)")
     ap.add_argument("--driver", default="c", choices=["c", "python"],
                     help="N>1: the C X-slab driver (direct stores into the neighbours' HBM; default) or the torch.distributed/NCCL protocol harness")
     ap.add_argument("--e2e-cycles", type=int, default=3, help="end-to-end cycles timed; the median is reported")
@@ -246,6 +342,8 @@ def main():
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)
+    if args.config:
+        return run_config(args)
 
     import numpy as np
     import torch
@@ -308,8 +406,8 @@ def main():
     step_gbs = bpc_step * act_local * K / (ms * 1e-3) / 1e9
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"BASELINE configs[3]: three cylinders, NS k-eps URANS (9 equations), flat, {args.nx}x{args.ny} cells per GPU "
-                                   f"({args.nx * world}x{args.ny} total), X-slabs", "model": args.model,
+            "config": {"workload": WORKLOAD if args.model == "keps" else f"three cylinders, model {args.model}, flat",
+                       "grid": f"{args.nx}x{args.ny} cells per GPU ({args.nx * world}x{args.ny} total), X-slabs", "model": args.model,
                        "active_cells": act, "total_cells": args.nx * args.ny * world, "seams": args.seams, "schedule": args.schedule if world > 1 else None, "rms_every": args.rms_every,
                        "multi_gpu_driver": (None if world == 1 else "C slab driver: peer-memory mailboxes over NVLink (hf2d_slab_run)" if use_c else "python SlabProtocol over NCCL"),
                        "tiles_per_gpu": {"plain": n_plain, "general": n_gen, "cols": tc, "rows": tr},

@@ -24,15 +24,19 @@
 #include "hf2d_stage1.cuh"
 
 #define TILE_H 32                 // rows per tile = lanes per warp
+// Block shape.  The general-tile launch runs on the side stream BESIDE K1a (k_stage1_tma), whose blocks hold 61 K of the
+// SM's 64 K registers: what the general blocks cost is the K1a blocks they displace.  Measured on the bench grid
+// (ms/step; K1a's share): 4 warps x 3 blocks, 156 registers: 2.010 (0.858); 8 warps, plain 2 blocks / general 3 blocks
+// at 80 registers: 1.935 (0.777); general 4 blocks at 64 registers (spills to L1): 1.929 (0.767); 16 warps: 1.960.
 #ifndef K1_WARPS
-#define K1_WARPS 4
+#define K1_WARPS 8
 #endif
 #define K1_THREADS (32 * K1_WARPS)
 #ifndef K1_MINB_PLAIN
-#define K1_MINB_PLAIN 3
+#define K1_MINB_PLAIN 2
 #endif
 #ifndef K1_MINB_GEN
-#define K1_MINB_GEN 3
+#define K1_MINB_GEN 4
 #endif
 
 __device__ __forceinline__ double warp_sum(double v) {

@@ -17,6 +17,7 @@
 //
 // Output directory: $OHF_DUMP_DIR (default ".").
 #include "libDEEPS2D/deeps2d_core.hpp"
+#include <unistd.h>
 #include <cstddef>
 #include <cstdio>
 #include <cstdlib>
@@ -167,6 +168,7 @@ void DEEPS2D_Run(ofstream* o_stream) {
         fwrite(J->GetMatrixPtr(), 1, (size_t)J->GetMatrixSize(), f);
         fclose(f);
     }
+    if (getenv("OHF_DUMP_ONLY")) _exit(0);       // bench.py --config: only the grid image is wanted, no CPU step, no writers
     const char* emv = getenv("OHF_EXIT_TIME");   // override the exit test: run until GlobalTime >= value
     if (emv) { MonitorIndex = 5; ExitMonitorValue = atof(emv); }
     const char* ns = getenv("OHF_NSTEP");        // override Nstep (the deck parser forces Nstep > NOutStep)
