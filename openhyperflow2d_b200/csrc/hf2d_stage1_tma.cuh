@@ -42,18 +42,20 @@ struct K1aMaps {                 // tensor maps of one grid (hf2d_gpu_upload_aos
 #define K1T_WARPS 4
 #endif
 #define K1T_THREADS (32 * K1T_WARPS)
-#define K1T_STAGE_OF(big, axi) ((big) ? ((axi) ? K1T_STAGE_BYTES : K1T_OFF_X2) : K1T_STAGE_BYTES_SMALL)   // flat grids have no F box: 14208
+// full stage: flat grids have no F box (14208 B), axisymmetric ones do (16128 B); four-box stage: 9856 B flat, + the F box
+// in the Src slot on axisymmetric grids (11904 B)
+#define K1T_STAGE_OF(big, axi) ((big) ? ((axi) ? K1T_STAGE_BYTES : K1T_OFF_X2) : ((axi) ? K1T_OFF_X1 : K1T_STAGE_BYTES_SMALL))
 #define K1T_SMEM_OF(big, axi) (K1T_WARPS * K1T_STAGE_OF(big, axi) + 64)
 // Two launch shapes.  The stage of a warp is what limits residency (bytes in flight AND warps to cover the FP64 dependent-issue
 // latency of the blending-factor divisions): 7 of the 9 equations of a flat k-eps grid need only the four basic boxes (9.9 KB),
-// so they run in a launch of their own with 5 blocks = 20 warps per SM and ONE code path for all seven (the equation index
+// (plus the F box on axisymmetric grids: 11.9 KB, 4 blocks), so they run in a launch of their own with 5 blocks = 20 warps per SM and ONE code path for all seven (the equation index
 // is a run-time plane offset: a third of the instruction footprint, the per-k switch had 13 % instruction-cache stalls);
 // the equations with Src / dSdy / F boxes keep the larger stage (14 KB flat: 4 blocks = 16 warps per SM; 16 KB axisymmetric: 3 blocks) and the compile-time switch.
 #ifndef K1T_MINB_BIG
 #define K1T_MINB_BIG(axi) ((axi) ? 3 : 4)
 #endif
 #ifndef K1T_MINB_SMALL
-#define K1T_MINB_SMALL 5
+#define K1T_MINB_SMALL(axi) ((axi) ? 4 : 5)
 #endif
 #ifndef K1T_BATCH
 #define K1T_BATCH 4               // columns whose blending-factor divisions run as one branch-free block
@@ -92,7 +94,7 @@ __device__ __forceinline__ void k1t_item(const Params& P, const StepState& st, c
     double* __restrict__ betak = P.beta + (long long)K * N;
     double* __restrict__ SNk = P.SN + (long long)K * N;
     constexpr unsigned f = eq_flags_c(ct, tt, KF, KC::ns);
-    static_assert(KT >= 0 || (f == 7u && !KC::axi), "run-time equation index: plain flags, flat grid");
+    static_assert(KT >= 0 || f == 7u, "run-time equation index: plain flags");
     const bool has_src = KT < 0 ? false : (KT >= 7 || P.has_src);
     // (the run-time-index launch is only used when no dS plane of equations 0..6 is tracked: hf2d_step.inc)
     const bool trk_x = KT < 0 ? false : ((P.need_dsx >> KF) & 1u) != 0, trk_y = KT < 0 ? false : ((P.need_dsy >> KF) & 1u) != 0;
@@ -103,7 +105,7 @@ __device__ __forceinline__ void k1t_item(const Params& P, const StepState& st, c
     const double* __restrict__ sBe = reinterpret_cast<const double*>(stage + K1T_OFF_BETA) + lane;
     const double* __restrict__ sSrc = reinterpret_cast<const double*>(stage + K1T_OFF_X0) + lane;
     const double* __restrict__ sDs = reinterpret_cast<const double*>(stage + K1T_OFF_X1) + lane;
-    const double* __restrict__ sF = reinterpret_cast<const double*>(stage + (DY2 ? K1T_OFF_X2 : K1T_OFF_X1)) + lane;
+    const double* __restrict__ sF = reinterpret_cast<const double*>(stage + (KT < 0 ? K1T_OFF_X0 : DY2 ? K1T_OFF_X2 : K1T_OFF_X1)) + lane;   // (four-box stage: F sits in the Src slot)
     // Columns in batches of K1T_BATCH: first every column's Stage-1 value (straight-line, independent), then the residual /
     // blending-factor divisions of the whole batch as ONE branch-free block with a single validity vote behind it, so that
     // the 2 divisions + 1 square root of K1T_BATCH columns overlap (each is a dependent chain of ~12 FP64 instructions;
@@ -175,7 +177,7 @@ __device__ __forceinline__ void k1t_item(const Params& P, const StepState& st, c
 // BIG = false: equations [k_first, k_first + k_count) within 0..6, four-box stage, run-time equation index;
 // BIG = true:  any equations, full stage, compile-time switch.
 template <class KC, bool BIG>
-__global__ void __launch_bounds__(K1T_THREADS, BIG ? K1T_MINB_BIG(KC::axi) : K1T_MINB_SMALL)
+__global__ void __launch_bounds__(K1T_THREADS, BIG ? K1T_MINB_BIG(KC::axi) : K1T_MINB_SMALL(KC::axi))
 k_stage1_tma(Params P, const K1aMaps* __restrict__ Mp, const int* __restrict__ tiles, int n_tiles, int n_sb, int s_half, int ds_half, int want_rms,
              int k_first, int k_count) {
     static_assert(KC::plain, "plain tiles only");
@@ -207,7 +209,7 @@ k_stage1_tma(Params P, const K1aMaps* __restrict__ Mp, const int* __restrict__ t
             unsigned bytes = (K1T_S_ROWS * (K1T_TI + 2) + 32 * (K1T_TI + 2) + K1T_B_ROWS * K1T_TI + 32 * K1T_TI) * 8;
             if (has_src) bytes += 32 * K1T_TI * 8;
             if (dy2) bytes += K1T_DS_ROWS * K1T_TI * 8;
-            if (BIG && KC::axi) bytes += 32 * K1T_TI * 8;
+            if (KC::axi) bytes += 32 * K1T_TI * 8;
             mbar_expect_tx(bar, bytes);
             const unsigned sbase = smem_u32(stage);
             tma_load_3d(sbase + K1T_OFF_S, &Mp->S[s_half], bar, j0 - 2, i0 - 1, k);
@@ -218,12 +220,12 @@ k_stage1_tma(Params P, const K1aMaps* __restrict__ Mp, const int* __restrict__ t
                 if (has_src) tma_load_3d(sbase + K1T_OFF_X0, &Mp->Src, bar, j0, i0, k);
                 if (dy2) tma_load_2d(sbase + K1T_OFF_X1, &Mp->dSy[ds_half], bar, j0, i0);
                 if (KC::axi) tma_load_3d(sbase + (dy2 ? K1T_OFF_X2 : K1T_OFF_X1), &Mp->F, bar, j0, i0, k);
-            }
+            } else if (KC::axi) tma_load_3d(sbase + K1T_OFF_X0, &Mp->F, bar, j0, i0, k);
         }
         __syncwarp();
         mbar_wait(bar, 0);
         if constexpr (!BIG) {
-            if constexpr (!KC::axi) k1t_item<KC, -1>(P, st, stage, lane, j, n_first, want_rms, acc, k);
+            k1t_item<KC, -1>(P, st, stage, lane, j, n_first, want_rms, acc, k);
         } else {
             switch (k) {
             case 0: k1t_item<KC, 0>(P, st, stage, lane, j, n_first, want_rms, acc, 0); break;

@@ -119,16 +119,17 @@ def test_gradient_members_come_back_for_a_restart(name):
 
 
 @pytest.mark.parametrize("case,exact,gpu_startup", [("ns_laminar", True, False), ("ns_prandtl_vd", False, False),
-                                                    ("ns_laminar", True, True), ("ns_prandtl_vd", False, True)])
+                                                    ("ns_laminar", True, True), ("ns_prandtl_vd", False, True),
+                                                    ("ns_keps_std", False, False), ("ns_keps_jl", False, False)])
 def test_restart_chain_through_the_reference_program(case, exact, gpu_startup, tmp_path, monkeypatch):
     """Swap-file checkpoint / restart, end to end: the reference program with its time loop on the GPU
     (oracle/_ref/ohf_gpu) runs 8 steps, leaves its swap file, is started AGAIN from it and runs 6 more; the unmodified
     program does the same.  The second start-up recomputes y_plus from the wall gradients of the first run's image
     (Recalc_y_plus) -- so y_plus, which the second run's damping functions read, agrees only if the GPU run's swap file
     carries the right dUdy / dVdx on the wall nodes (van Driest: the mixing length is a function of y_plus).
-    Decks with isTurbulenceReset = 1 are NOT covered: their restart re-runs FillNode2D(0,1) on every node with the
-    gradient members of the records (ScanArea, deeps2d_core.cpp:2186-2205), which the download does not restore
-    (DESIGN.md section 2)."""
+    The k-eps decks set isTurbulenceReset = 1: their restart re-runs FillNode2D(0,1) on every node with the gradient
+    members of the records (ScanArea, deeps2d_core.cpp:2186-2205) -- all 18 of them come back with the download since
+    the last step of every step call writes them (hf2d_gpu_keep_gradients, the default)."""
     import os
     import subprocess
     import test_shim_dropin as D

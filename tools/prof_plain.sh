@@ -8,7 +8,7 @@ mkdir -p gpurun_out
 cmd="python bench.py --steps 4 --warmup 3 --no-cpu --no-e2e --model $model"
 $cmd > gpurun_out/${tag}_plain.log 2>&1 || { tail -5 gpurun_out/${tag}_plain.log; exit 1; }
 rep=/tmp/${tag}_prof.ncu-rep
-ncu --set full --clock-control none --import-source on -k 'regex:k_(stage1_plain|stage1_tma|point|flux|step_plain)' -s 20 -c 5 -f -o ${rep%.ncu-rep} $cmd > gpurun_out/${tag}_ncu.log 2>&1
+ncu --set full --clock-control none --import-source on -k 'regex:k_(stage1_plain|stage1_tma|point|flux|step_plain)' -s 24 -c 8 -f -o ${rep%.ncu-rep} $cmd > gpurun_out/${tag}_ncu.log 2>&1
 ncu -i $rep --page raw --csv > gpurun_out/${tag}_raw.csv 2>/dev/null
 ncu -i $rep --page source --csv 2>/dev/null | gzip -9 > gpurun_out/${tag}_source.csv.gz
 ls -la $rep gpurun_out/${tag}_raw.csv gpurun_out/${tag}_source.csv.gz
