@@ -27,7 +27,7 @@ else:
     out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", "regex:" + fn], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
 # several launches may follow each other: take the first block whose demangled name holds `sub`
-k_i = next(i for i, r in enumerate(rows) if r and r[0] == "Kernel Name" and sub in r[1])
+k_i = next(i for i, r in enumerate(rows) if r and r[0] == "Kernel Name" and sub in r[1] and (fn + "<") in r[1].replace(" ", "") + "<")
 hdr_i = next(i for i, r in enumerate(rows) if i > k_i and r and r[0] == "Address")
 hdr = rows[hdr_i]
 body = []
