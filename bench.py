@@ -392,7 +392,7 @@ def main():
     peak, peak_src = peaks()
     kb = kernel_bytes_per_cell(args.model)
     kms = {"k1a": kt["k1a_plain_ms"], "k1b": kt["k1b_plain_ms"], "k2": kt["k2_plain_ms"]}
-    kname = {"k1a": "k_stage1_plain<plain tiles> (Stage 1 + blending factor)", "k1b": "k_point<plain tiles> (EOS, chemistry, tables, dt)",
+    kname = {"k1a": "k_stage1_tma<plain tiles> (K1a: Stage 1 + residual + blending factor, TMA-staged)", "k1b": "k_point<plain tiles> (EOS, chemistry, tables, dt)",
              "k2": "k_flux<plain tiles> (gradients, turbulence, fluxes)"}
     kfrac = {q: (kb[q] * plain_cells / (kms[q] * 1e-3) / 1e9 / peak if kms[q] > 0 else 0.0) for q in kb}
     top = max(kms, key=lambda q: kms[q])          # the dominant kernel = the longest of the three
