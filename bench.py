@@ -186,7 +186,7 @@ def reference_arm(args):
     nsteps = int(min(max(4 * (args.warmup + args.steps), 100), 200))
     r = run_reference_binary("ohf_omp", nx, ny, nsteps, nthreads)
     if r is not None:
-        ser = run_reference_binary("ohf_serial", nx, ny, min(nsteps, 100), 1)
+        ser = run_reference_binary("ohf_serial", nx, ny, 40, 1)
         v, kind, cores, ms = r[0], "reference", nthreads, 1e3 / r[2]
         how = (f"unmodified reference, OpenMP build (oracle/_ref/ohf_omp, OMP_NUM_THREADS={nthreads}), three-cylinder k-eps deck {nx}x{ny} "
                f"({r[1]} active cells), one run of {nsteps} steps, the solver's own 'average speed' line"

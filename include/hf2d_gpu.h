@@ -252,7 +252,10 @@ int  hf2d_gpu_residual_sums(hf2d_gpu* h, double rms[HF2D_NEQ], double sum_div[HF
  * The wall nodes' dUdy, dVdx are those of the last step (or of the records as uploaded, before any step).  The device
  * y_plus plane the step reads is updated in place; y_plus (nx*ny doubles, may be NULL) receives the plane -- entries of
  * unset / solid nodes are the plane as uploaded.  HF2D_EINVAL if some node's (i_wall, j_wall) is not a wall node (a deck
- * without walls: the reference then reads node (0,0)'s gradients, which are not kept); y+ of those nodes is unchanged. */
+ * without walls: the reference then reads node (0,0)'s gradients, which are not kept); y+ of those nodes is unchanged.
+ * i_wall holds LOCAL columns of this handle's grid: the output of hf2d_gpu_set_min_distance_to_wall_slab (GLOBAL columns) is
+ * not accepted here -- a host that cuts the grid into slabs refreshes y+ on the undivided grid before it uploads the slabs
+ * (the reference does it on rank 0 only as well, deeps2d_core.cpp:1723-1726). */
 int  hf2d_gpu_recalc_y_plus(hf2d_gpu* h, const int* i_wall, const int* j_wall, double* y_plus);
 
 /* ---------------------------------------------------------------------------------------------------------------------

@@ -289,3 +289,31 @@ def test_slab_cuts_balance_active_nodes():
     # degenerate: nothing active -> minimum widths still respected
     cuts = slab_cuts(np.zeros((8, 4), dtype=np.uint64), 4)
     assert all(i1 - i0 >= 2 for i0, i1 in cuts) and cuts[-1][1] == 8
+
+
+def test_c_slab_cuts_match_the_python_restatement():
+    """hf2d_slab_cuts (csrc/hf2d_slab.inc, pure host code: runs without a GPU) against multigpu.slab_cuts on flag-word
+    patterns with solid blocks, unset columns and degenerate quotas; every column owned, no slab narrower than min_cols."""
+    from golden_util import LAYOUT
+    from openhyperflow2d_b200 import aos, cabi
+    from openhyperflow2d_b200.multigpu import slab_cuts
+    rng = np.random.default_rng(7)
+    dt = aos.ref_dtype(LAYOUT)
+    for nx, ny in ((40, 12), (97, 33), (16, 5)):
+        for trial in range(6):
+            J = np.zeros((nx, ny), dtype=dt)
+            ct = np.full((nx, ny), 0x80000000, dtype=np.uint64)
+            if trial >= 1:      # a solid body on one side: the slabs there must be wider
+                ct[: nx // 3, : (ny * (trial % 3 + 1)) // 4] |= 0x40000000
+            if trial >= 3:      # columns that are not set at all
+                ct[rng.integers(0, nx, size=nx // 5)] = 0
+            if trial == 5:
+                ct[:] = 0x80000000 | 0x40000000        # nothing active: the cuts fall back to the column limits
+            J["CT"] = ct
+            for world in (1, 2, 3, 4, 8):
+                if nx < 2 * world:
+                    continue
+                got = cabi.slab_cuts(J, LAYOUT, world)
+                want = slab_cuts(ct, world)
+                assert got == [want[0][0]] + [b for _, b in want], (nx, ny, trial, world, got, want)
+                assert got[0] == 0 and got[-1] == nx and all(b - a >= 2 for a, b in zip(got, got[1:]))
