@@ -421,6 +421,18 @@ def main():
             "gpu_launches": int(runner.launches_last), "clocks": clocks}
     if rank == 0 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(args.model)
+    if world == 1 and not args.no_cpu and args.model == "keps":
+        # like for like with the reference arm: the same deck on the reference arm's grid (its start-up limits that grid,
+        # reference_arm()), device-timed; 0.5 M cells fill a B200 only partly (launch-latency bound)
+        Js, cs_, ls = gridgen.three_cylinders(REF_NX, REF_NY, model=args.model)
+        ss = cabi.Solver(cs_, ls, device=local, rms_every=args.rms_every)
+        ss.upload_aos(Js)
+        ss.step(20)
+        rs = ss.step_continue(200)
+        a_s = ss.active_cells()[0]
+        ss.close()
+        line["same_grid_as_reference_arm"] = {"grid": f"{REF_NX}x{REF_NY}", "active_cells": a_s, "steps": 200, "ms_per_step": rs.gpu_ms / 200,
+                                              "value": a_s * 200 / (rs.gpu_ms * 1e-3), "unit": UNIT}
     if parity is not None:
         line["parity"] = parity
     if not args.no_e2e:
