@@ -208,14 +208,16 @@ def kernel_bytes_per_cell(model, axi=False):
     plane a kernel owns read once / written once, neighbour reads served on chip.
       K1a k_stage1_plain: reads S, beta, A, B [Neq each], Src [Neq-7], (F [Neq] axisymmetric), (dSdy[eps] k-eps); writes SN, beta [Neq each], (dSdy[eps])
       K1b k_point:        reads SN [Neq], CP, R, k; writes S [Neq], U, V, Tg, k, p, R, CP (+ mu, lam NS)
-      K2  k_flux:         reads S_new [Neq], SN[4..6], U, V, Tg, p, k (new), S_old[0,4..Neq-1], U, V, Tg (old), CP, R, k (old)
+      K2  k_flux:         reads S_new [Neq], (SN[4..6] where chemistry changed them), U, V, Tg, p, k (new), S_old[0,4..Neq-1], U, V, Tg (old), CP, R, k (old)
                           (+ mu, lam, mu_t, l_min NS); writes A, B [Neq each], (F), Src [Neq-7], mu_t"""
     neq = {"keps": 9, "sa": 8}.get(model, 7)
     ns = model != "euler"
     ke = 1 if model == "keps" else 0
     k1a = (4 * neq + (neq - 7) + (neq if axi else 0) + ke) + (2 * neq + ke)
     k1b = (neq + 3) + (neq + 7 + (2 if ns else 0))
-    k2 = (neq + 3 + 5 + (neq - 3) + 3 + 3 + (4 if ns else 0)) + (2 * neq + (neq if axi else 0) + (neq - 7) + (1 if ns else 0))
+    # (SN[4..6] -- the species densities before chemistry -- are read only on tiles where chemistry changed them, Params::tile_inert:
+    #  nowhere on the air-only bench grid, so they are not counted)
+    k2 = (neq + 0 + 5 + (neq - 3) + 3 + 3 + (4 if ns else 0)) + (2 * neq + (neq if axi else 0) + (neq - 7) + (1 if ns else 0))
     return {"k1a": 8.0 * k1a, "k1b": 8.0 * k1b, "k2": 8.0 * k2}
 
 

@@ -23,6 +23,9 @@
 #ifndef K2_MINB_PLAIN
 #define K2_MINB_PLAIN 3
 #endif
+#ifndef K2_INERT
+#define K2_INERT 1                // 0: always read the species densities before chemistry from the shadow planes
+#endif
 #ifndef K2_MINB_GEN
 #define K2_MINB_GEN 3
 #endif
@@ -68,6 +71,7 @@ k_flux(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI, i
         } else { DivExact e; ph(e); }
     };
 
+    const bool inert = K2_INERT && KC::plain && P.tile_inert && P.tile_inert[tile] != 0;      // warp-uniform (Params::tile_inert)
     NbState carry;   // new state of the left neighbour = this thread's own node of the previous column
     carry.rho = carry.y4 = carry.y5 = carry.y6 = carry.s7 = carry.s8 = carry.U = carry.V = carry.Tg = 0.;
     bool have_carry = false;
@@ -94,7 +98,7 @@ k_flux(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI, i
                 for (int k = 0; k < 7; k++) pf(&P.S_out[(long long)k * N + m]);
                 if (TURB_C) { pf(&P.S_out[7 * N + m]); pf(&P.S_out[8 * N + m]); }
                 pf(&P.U_out[m]); pf(&P.V_out[m]); pf(&P.Tg_out[m]); pf(&P.p_out[m]); pf(&P.kg_out[m]);
-                pf(&P.SN[4 * N + m]); pf(&P.SN[5 * N + m]); pf(&P.SN[6 * N + m]);
+                if (!inert) { pf(&P.SN[4 * N + m]); pf(&P.SN[5 * N + m]); pf(&P.SN[6 * N + m]); }
                 if (KC::ns) {
                     pf(&P.CP_in[m]); pf(&P.R_in[m]); pf(&P.mu_in[m]); pf(&P.kg_in[m]); pf(&P.mu_t[m]); pf(&P.lam_in[m]);
                     if (KC::ttc != 0) pf(&P.l_min[m]);
@@ -125,6 +129,8 @@ k_flux(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI, i
             L.S[7] = mine.s7; L.S[8] = mine.s8;
             if (!turbN || !(KC::plain || hasturb)) { L.S[7] = 0.; L.S[8] = 0.; }
             // species densities as FillNode2D sees them: committed, before chemistry
+            if (inert) { L.S[4] = mine.y4; L.S[5] = mine.y5; L.S[6] = mine.y6; }      // the same bits as the shadow planes hold
+            else
 #pragma unroll
             for (int k = 4; k < 7; k++) {
                 const bool com = KC::plain ? true : (act && eq_committed(ct, tt, k, KC::ns));
@@ -239,6 +245,8 @@ k_flux(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI, i
             Local L;
 #pragma unroll
             for (int k = 0; k < 4; k++) L.S[k] = P.S_out[(long long)k * N + n];
+            if (inert) { L.S[4] = mine.y4; L.S[5] = mine.y5; L.S[6] = mine.y6; }
+            else
 #pragma unroll
             for (int k = 4; k < 7; k++) {
                 const bool com = KC::plain ? true : (act && eq_committed(ct, tt, k, KC::ns));

@@ -58,7 +58,9 @@ template <int NS, int AXI, int TTC> struct KCfg {
 };
 
 #ifndef K1B_LAZY
-#define K1B_LAZY 0                // 1: plain tiles fetch last step's U, V, Tg, p only where FillNode2D returns early (32 B/cell less, but the dependent branch costs more than the bytes: 0.444 vs 0.416 ms)
+#define K1B_LAZY 2                // plain tiles fetch last step's U, V, Tg, p only where FillNode2D returns early (S[Rho] == 0 or k < 1: never on
+                                  // a sane grid).  1 = decided per lane: SLOWER than fetching them always (0.444 vs 0.416 ms: divergent branch
+                                  // in front of four dependent loads); 2 = one warp-uniform decision (__any_sync): 0.429 -> 0.422 ms.  0 = always.
 #endif
 // Where a node's own inputs come from: last step's planes.
 struct GlobalLoad {
@@ -94,7 +96,7 @@ __device__ __forceinline__ void local_rest(D& dv, const LD& ld, const Params& P,
     // Last step's U, V, Tg, p survive only where FillNode2D returns early (S[Rho] == 0 or k < 1) or a CONST flag pins them:
     // an unflagged interior node overwrites all four, so the plain-tile kernels fetch them only in the early-return case
     // (4 planes = 32 B per cell that the bulk of the grid never reads).
-    if (!KC::plain || !K1B_LAZY || (L.S[iRho] == 0) || (kg_old < 1)) {
+    if (!KC::plain || !K1B_LAZY || (K1B_LAZY == 2 ? __any_sync(0xffffffffu, (L.S[iRho] == 0) || (kg_old < 1)) : ((L.S[iRho] == 0) || (kg_old < 1)))) {   // (2: one warp-uniform decision)
         L.Uo = ld.U(); L.Vo = ld.V(); L.Tgo = ld.Tg();
         if (FULL) L.po = ld.p();
     } else { L.Uo = L.Vo = L.Tgo = 0.; if (FULL) L.po = 0.; }

@@ -109,6 +109,7 @@ k_point(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI, 
     constexpr int NE_C = KC::plain ? (!KC::ns ? 7 : (KC::ttc & TCT_Prandtl_Model) ? 7 : (KC::ttc & TCT_k_eps_Model) ? 9 : (KC::ttc & TCT_SA_Model) ? 8 : 7) : 0;
     constexpr bool TURB_C = KC::plain && KC::ns && (KC::ttc & (TCT_k_eps_Model | TCT_SA_Model)) != 0;
 
+    bool tile_same = true;         // plain tiles: chemistry left S[4..6] of every node visited so far unchanged (Params::tile_inert)
     for (int i = i0; i < i1; i++) {
         const long long n = valid_j ? (long long)i * ny + j : 0;
         uint32_t ct, tt;
@@ -266,6 +267,7 @@ k_point(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI, 
         // ====== own-node half of FillNode2D + CalcChemicalReactions + dt: the node's new state ======
         const GlobalLoad ld{P, n};
         const unsigned long long r_dt0 = r_dt, r_err0 = r_err;
+        bool col_same = true;
         run([&](auto& dv) {
             r_dt = r_dt0; r_err = r_err0;
             if (!upd) return;
@@ -322,12 +324,18 @@ k_point(Params P, const int* __restrict__ tiles, int n_tiles, int n_sb, int TI, 
             }
             P.S_out[0 * N + n] = L.S[0]; P.S_out[1 * N + n] = L.S[1]; P.S_out[2 * N + n] = L.S[2]; P.S_out[3 * N + n] = L.S[3];
             P.S_out[4 * N + n] = s4; P.S_out[5 * N + n] = s5; P.S_out[6 * N + n] = s6;
+            if (KC::plain) col_same = d2bits(s4) == d2bits(sn[4]) && d2bits(s5) == d2bits(sn[5]) && d2bits(s6) == d2bits(sn[6]);
             if (KC::plain ? TURB_C : hasturb) { P.S_out[7 * N + n] = L.S[7]; P.S_out[8 * N + n] = L.S[8]; }
             P.U_out[n] = L.U; P.V_out[n] = L.V; P.Tg_out[n] = L.Tg;
             P.kg_out[n] = L.kg; P.p_out[n] = L.p;
             P.R_out[n] = R_new; P.CP_out[n] = CP_new;
             if (KC::ns) { P.mu_out[n] = mu_new; P.lam_out[n] = have_lam ? lam_new : P.lam_in[n]; }
         });
+        tile_same = tile_same && col_same;
+    }
+    if constexpr (KC::plain) {
+        const bool all_same = __all_sync(0xffffffffu, tile_same);
+        if (lane == 0 && t_idx < n_tiles && P.tile_inert) P.tile_inert[tile] = all_same ? 1 : 0;
     }
 
     // ---- block reduction of the step's scalars: warp REDUX/shuffles -> shared memory -> at most one atomic per block
