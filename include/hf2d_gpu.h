@@ -258,6 +258,18 @@ int  hf2d_gpu_residual_sums(hf2d_gpu* h, double rms[HF2D_NEQ], double sum_div[HF
  * (the reference does it on rank 0 only as well, deeps2d_core.cpp:1723-1726). */
 int  hf2d_gpu_recalc_y_plus(hf2d_gpu* h, const int* i_wall, const int* j_wall, double* y_plus);
 
+/* The body of the reference's Tecplot snapshot -- SaveData2D (libDEEPS2D/deeps2d_core.cpp:2589-2673, called through
+ * DataSnapshot :2494-2516 at the end of every output cycle, :1773-1780): one line of 16 "%g" columns per node, j outer, i inner
+ * -- formatted on the device from the current state, byte for byte what the host writer prints from the downloaded J (67 M
+ * lines, ~7 GB of text at 16k x 4k).  type = the reference's ioMode (0 append / Tecplot, 1 rewrite: a blank line after each row);
+ * dx_out, dy_out = (dx*MaxX)/(MaxX-1), (dy*MaxY)/(MaxY-1) as the caller's compiler evaluates them (:2618-2619).  The two
+ * title lines (:2607-2616) stay the caller's.  Covers is_Cx_calc == 0 and is_p_asterisk_out == 0 on an undivided grid whose record
+ * image is resident in HBM; otherwise HF2D_EINVAL / HF2D_ESTATE and the caller runs the host writer.
+ *   hf2d_gpu_tecplot_format(...)  -> *bytes = length of the text, kept on the device;
+ *   hf2d_gpu_tecplot_fetch(...)   -> copies it into host_text (bytes long) and releases it. */
+int  hf2d_gpu_tecplot_format(hf2d_gpu* h, const hf2d_node_layout* layout, int type, double dx_out, double dy_out, size_t* bytes);
+int  hf2d_gpu_tecplot_fetch(hf2d_gpu* h, char* host_text, size_t bytes);
+
 /* ---------------------------------------------------------------------------------------------------------------------
  * X-slab multi-GPU driver (csrc/hf2d_slab.inc).  Replaces, for the GPU path, the reference's multi-rank contract:
  *   DEEPS2D_Run(o_stream, pJ, pC, rank, last_rank, x0)          libDEEPS2D/deeps2d_core.hpp:206-212, call hf2d_start.cpp:285

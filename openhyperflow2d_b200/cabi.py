@@ -68,7 +68,7 @@ EXPORTS = ["hf2d_gpu_last_error", "hf2d_gpu_device_count", "hf2d_gpu_create", "h
            "hf2d_gpu_halo_unpack_lane", "hf2d_gpu_edge_tile_counts", "hf2d_gpu_set_min_distance_to_wall", "hf2d_gpu_set_global_time", "hf2d_gpu_recalc_y_plus", "hf2d_gpu_residual_sums", "hf2d_gpu_set_min_distance_to_wall_slab", "hf2d_gpu_keep_gradients",
            "hf2d_gpu_wall_distance_noalloc", "hf2d_slab_cuts", "hf2d_slab_create", "hf2d_slab_destroy", "hf2d_slab_solver", "hf2d_slab_columns",
            "hf2d_slab_ipc_handle_bytes", "hf2d_slab_ipc_handle", "hf2d_slab_connect_ipc", "hf2d_slab_connect_local", "hf2d_slab_upload",
-           "hf2d_slab_download", "hf2d_slab_upload_local", "hf2d_slab_download_local", "hf2d_slab_run", "hf2d_slab_read_node"]
+           "hf2d_slab_download", "hf2d_slab_upload_local", "hf2d_slab_download_local", "hf2d_slab_run", "hf2d_slab_read_node", "hf2d_gpu_tecplot_format", "hf2d_gpu_tecplot_fetch"]
 
 
 def lib():
@@ -125,6 +125,8 @@ def lib():
         L.hf2d_gpu_launch_count.restype = C.c_ulonglong
         L.hf2d_gpu_keep_gradients.argtypes = [C.c_void_p, C.c_int]
         L.hf2d_gpu_wall_distance_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.hf2d_gpu_tecplot_format.argtypes = [C.c_void_p, C.POINTER(NodeLayout), C.c_int, C.c_double, C.c_double, C.POINTER(C.c_size_t)]
+        L.hf2d_gpu_tecplot_fetch.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
         L.hf2d_slab_cuts.argtypes = [C.c_void_p, C.POINTER(NodeLayout), C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
         L.hf2d_slab_create.argtypes = [C.POINTER(Cfg), C.c_int, C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]
         L.hf2d_slab_destroy.argtypes = [C.c_void_p]
@@ -362,6 +364,14 @@ class Solver:
         (nx*ny doubles / int32 / int32 / uint8) of the caller.  At most 16384 wall nodes."""
         walls = np.ascontiguousarray(walls, dtype=np.int32).reshape(-1, 2)
         _ck(lib().hf2d_gpu_wall_distance_noalloc(self._h, walls.ctypes.data, len(walls), float(x0), dev_l_min, dev_i_wall, dev_j_wall, dev_status))
+
+    def tecplot_body(self, type_: int, dx_out: float, dy_out: float) -> bytes:
+        """hf2d_gpu_tecplot_format + _fetch: the body of SaveData2D for the current state, formatted on the device."""
+        n = C.c_size_t()
+        _ck(lib().hf2d_gpu_tecplot_format(self._h, C.byref(self.layout), int(type_), float(dx_out), float(dy_out), C.byref(n)))
+        buf = C.create_string_buffer(max(n.value, 1))
+        _ck(lib().hf2d_gpu_tecplot_fetch(self._h, buf, n.value))
+        return buf.raw[:n.value]
 
     def set_min_distance_to_wall(self, walls, x0: float = 0.0):
         """SetMinDistanceToWall2D(J, WallNodes, x0) on the uploaded grid (deeps2d_core.cpp:4783-4832).  walls: (n, 2) int

@@ -65,6 +65,7 @@ struct hf2d_gpu {
     uint64_t launches;
     void* d_stage; size_t stage_bytes;
     void* d_image; size_t image_bytes;   // the raw record image, resident when it fits (hf2d_io.inc)
+    char* d_text; size_t text_bytes;     // formatted Tecplot body waiting to be fetched (hf2d_tecplot.inc)
     double bytes_per_cell;
     // tiles (hf2d_point.cuh): TI columns x TILE_H rows, one warp each
     int TI, n_sb, n_tx;
@@ -102,6 +103,8 @@ template <class T> static int dalloc(hf2d_gpu* h, T** p, size_t count, bool zero
     return 0;
 }
 
+static int create_impl(const hf2d_cfg* cfg, int device, hf2d_gpu* h);
+extern "C" int hf2d_gpu_destroy(hf2d_gpu* h);
 extern "C" int hf2d_gpu_create(const hf2d_cfg* cfg, int device, hf2d_gpu** out) {
     if (!cfg || !out) return fail(HF2D_EINVAL, "null argument");
     if (cfg->nx < 1 || cfg->ny < 1) return fail(HF2D_EINVAL, "bad grid %d x %d", cfg->nx, cfg->ny);
@@ -112,7 +115,13 @@ extern "C" int hf2d_gpu_create(const hf2d_cfg* cfg, int device, hf2d_gpu** out) 
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(HF2D_ECUDA, "no CUDA device: this library has no CPU fallback");
     if (device < 0 || device >= ndev) return fail(HF2D_EINVAL, "device %d out of range (%d devices)", device, ndev);
     CK(cudaSetDevice(device));
-    hf2d_gpu* h = new hf2d_gpu();
+    hf2d_gpu* h = new hf2d_gpu();        // (value-initialised: every handle member is null until it is created)
+    const int rc = create_impl(cfg, device, h);
+    if (rc) { const std::string msg = g_err; hf2d_gpu_destroy(h); snprintf(g_err, sizeof(g_err), "%s", msg.c_str()); return rc; }   // no leak on an early error
+    *out = h;
+    return HF2D_OK;
+}
+static int create_impl(const hf2d_cfg* cfg, int device, hf2d_gpu* h) {
     h->cfg = *cfg; h->device = device; h->uploaded = false; h->launches = 0; h->d_stage = nullptr; h->stage_bytes = 0; h->d_image = nullptr; h->image_bytes = 0;
     h->d_nlist = h->d_wall_list = nullptr; h->n_nlist = h->n_wall = 0; h->n_active = 0;
     for (int t = 0; t < HF2D_NTABLES; t++) { h->cfg.tab[t].x = nullptr; h->cfg.tab[t].y = nullptr; }
@@ -163,22 +172,24 @@ extern "C" int hf2d_gpu_create(const hf2d_cfg* cfg, int device, hf2d_gpu** out) 
     h->last_iter_cycle = cfg->last_iter;
     h->rms_every = cfg->NOutStep; h->prepass_done = false; h->timing = false; h->tn[0] = h->tn[1] = h->tn[2] = 0;
     h->TI = 16; h->n_sb = h->n_tx = 0; h->d_tiles_plain = h->d_tiles_gen = nullptr; h->n_plain = h->n_gen = 0; h->n_plain_edge = h->n_gen_edge = 0; h->s2_pending = false; h->n_chains_local = 0; h->d_nlist_seam = nullptr; h->n_nlist_seam = 0; h->prepass_local_done = false; h->ahead = false; h->plain_ttc = -1; h->tma_ok = false; h->k1t_all_big = false; h->d_maps = nullptr; h->S_half0 = nullptr; h->dSy8_half0 = nullptr; h->keep_grads = true; h->grads_this_step = false; h->grads_valid = false;
-    *out = h;
     return HF2D_OK;
 }
 
 extern "C" int hf2d_gpu_destroy(hf2d_gpu* h) {
     if (!h) return HF2D_OK;
     cudaSetDevice(h->device);
-    cudaStreamSynchronize(h->stream);
+    if (h->stream) cudaStreamSynchronize(h->stream);
     for (void* p : h->allocs) cudaFree(p);
     for (auto& c : h->cache) cudaFree(c.second);
     if (h->d_stage) cudaFree(h->d_stage);
     if (h->d_image) cudaFree(h->d_image);
+    if (h->d_text) cudaFree(h->d_text);
     if (h->h_st) cudaFreeHost(h->h_st);
-    cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
+    // (a handle whose creation failed half-way holds nulls)
+    for (cudaEvent_t e : {h->ev0, h->ev1, h->ev_fork_c, h->ev_join_c, h->ev_fork, h->ev_join}) if (e) cudaEventDestroy(e);
     for (int a = 0; a < 3; a++) for (int b = 0; b < 2; b++) for (cudaEvent_t e : h->tev[a][b]) cudaEventDestroy(e);
-    cudaStreamDestroy(h->stream0); cudaStreamDestroy(h->stream_b); cudaStreamDestroy(h->stream_c); cudaEventDestroy(h->ev_fork_c); cudaEventDestroy(h->ev_join_c); cudaEventDestroy(h->ev_fork); cudaEventDestroy(h->ev_join);
+    for (cudaStream_t st : {h->stream0, h->stream_b, h->stream_c}) if (st) cudaStreamDestroy(st);
+    cudaGetLastError();
     delete h;
     return HF2D_OK;
 }
@@ -252,3 +263,4 @@ extern "C" int hf2d_gpu_keep_gradients(hf2d_gpu* h, int enable) {
 #include "hf2d_step.inc"
 #include "hf2d_walldist.inc"
 #include "hf2d_noalloc.inc"
+#include "hf2d_tecplot.inc"

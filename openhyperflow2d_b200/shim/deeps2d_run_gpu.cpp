@@ -73,6 +73,32 @@ static void eng_destroy() {
     for (int r = 0; r < g_nslab; r++) hf2d_slab_destroy(g_slab[r]);
 }
 
+// ---- the Tecplot snapshot with its body formatted on the device (HF2D_GPU_TECPLOT=1) ----
+// DataSnapshot (deeps2d_core.cpp:2494-2516) = CutFile if rewriting, OpenData (append mode), SaveData2D, close.  The two title
+// lines are written here exactly as SaveData2D writes them (:2594-2616); the 16-column body comes from
+// hf2d_gpu_tecplot_format / _fetch.  Falls back to the reference's own DataSnapshot where the formatter does not apply
+// (is_Cx_calc, is_p_asterisk_out, several slabs, no resident image).
+extern int is_p_asterisk_out;
+static int g_gpu_tecplot = 0;
+static void snapshot(char* filename, WRITE_MODE mode, const hf2d_node_layout* lay) {
+    size_t bytes = 0;
+    const FP dx_out = (dx * MaxX) / (MaxX - 1), dy_out = (dy * MaxY) / (MaxY - 1);       // :2618-2619
+    if (!g_gpu_tecplot || g_nslab || is_Cx_calc || is_p_asterisk_out ||
+        hf2d_gpu_tecplot_format(g_h, lay, (int)mode, dx_out, dy_out, &bytes)) { DataSnapshot(filename, mode); return; }
+    char* text = (char*)malloc(bytes ? bytes : 1);
+    if (!text || hf2d_gpu_tecplot_fetch(g_h, text, bytes)) { free(text); DataSnapshot(filename, mode); return; }
+    if (mode) CutFile(filename);
+    ofstream* out = OpenData(filename);
+    char t1[1024] = {0}, t2[256] = {0};
+    snprintf(t1, 1024, "VARIABLES = X, %s, U, V, T, p, Rho, Y_fuel, Y_ox, Y_cp, Y_i, %s, Mach, l_min, y+, Cp\n",
+             FlowNode2D<FP, NUM_COMPONENTS>::FT == 1 ? "R" : "Y", "mu_t/mu");
+    snprintf(t2, 256, "ZONE T=\"Time: %g sec.\" I= %i J= %i F=POINT\n", GlobalTime, MaxX, MaxY);
+    *out << t1 << t2;
+    out->write(text, (std::streamsize)bytes);
+    out->close();
+    free(text);
+}
+
 static void die(ofstream* f, const char* what) {
     *f << "\nhf2d_gpu: " << what << ": " << hf2d_gpu_last_error() << "\n" << flush;
     Abort_OpenHyperFLOW2D();
@@ -222,6 +248,8 @@ void DEEPS2D_Run(ofstream* f_stream) {
         if (hf2d_gpu_upload_aos(h, J->GetMatrixPtr(), &lay, pinned)) die(f_stream, "upload");
     }
     *f_stream << "hf2d_gpu: DEEPS2D time loop on the GPU (" << MaxX << "x" << MaxY << " nodes)\n" << flush;
+    g_gpu_tecplot = getenv("HF2D_GPU_TECPLOT") && atoi(getenv("HF2D_GPU_TECPLOT"));
+    if (g_gpu_tecplot) *f_stream << "hf2d_gpu: Tecplot snapshots formatted on the GPU\n" << flush;
 
     I = 0; isRun = 1;
     FP max_RMS = 0.; int k_max_RMS = -1;
@@ -296,10 +324,10 @@ void DEEPS2D_Run(ofstream* f_stream) {
         }
         gettimeofday(&stop, NULL);
         *f_stream << "\nSave current results in file " << OutFileName << "...\n" << flush;
-        DataSnapshot(OutFileName, WM_REWRITE);
+        snapshot(OutFileName, WM_REWRITE, &lay);
         if ((I / NSaveStep) * NSaveStep == I) {
             *f_stream << "Add current results to transient solution file " << TecPlotFileName << "...\n" << flush;
-            DataSnapshot(TecPlotFileName, WM_APPEND);
+            snapshot(TecPlotFileName, WM_APPEND, &lay);
         }
         I++;
         const FP c_time = (FP)(stop.tv_sec - start.tv_sec) + (FP)(stop.tv_usec - start.tv_usec) * 1.e-6;
@@ -341,7 +369,7 @@ void DEEPS2D_Run(ofstream* f_stream) {
         if (MonitorIndex < 5) MonitorCondition = (max_RMS > ExitMonitorValue) ? 1 : 0;
         else MonitorCondition = (GlobalTime < ExitMonitorValue) ? 1 : 0;
     } while (MonitorCondition);
-    DataSnapshot(OutFileName, WM_REWRITE);
+    snapshot(OutFileName, WM_REWRITE, &lay);
     if (pinned) hf2d_gpu_unpin_host(J->GetMatrixPtr());
     eng_destroy();
     *f_stream << "\nReady. Computation finished.\n" << flush;
