@@ -4,9 +4,11 @@
 square root are nvcc's default for double.  -lineinfo so ncu's source page maps to the .cuh files."""
 from __future__ import annotations
 
+import hashlib
 import os
 import shutil
 import subprocess
+import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
@@ -23,13 +25,31 @@ def _newest_src() -> float:
     return t
 
 
+def source_hash() -> str:
+    """sha256 over the sources the library is built from (csrc/ and include/), written beside the library at build time."""
+    h = hashlib.sha256()
+    for root in (CSRC, os.path.join(os.path.dirname(HERE), "include")):
+        for f in sorted(os.listdir(root)):
+            h.update(f.encode())
+            with open(os.path.join(root, f), "rb") as fh:
+                h.update(fh.read())
+    return h.hexdigest()
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
     if not force and os.path.exists(SO) and os.path.getmtime(SO) >= _newest_src():
         return SO
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     if not os.path.exists(nvcc):
+        # a box without a toolchain: the prebuilt library that travelled with the snapshot -- but only if it was built from
+        # THESE sources (a run on an old library must not pass unnoticed)
         if os.path.exists(SO):
-            return SO   # GPU box without a toolchain: use the prebuilt library that travelled with the snapshot
+            want = source_hash()
+            have = open(SO + ".srchash").read().strip() if os.path.exists(SO + ".srchash") else "(no hash recorded)"
+            if have != want:
+                raise RuntimeError(f"nvcc not found and the prebuilt {SO} was built from other sources (library {have[:12]}, tree {want[:12]})")
+            print(f"openhyperflow2d_b200: no nvcc here, using the prebuilt {SO} (sources {want[:12]})", file=sys.stderr)
+            return SO
         raise RuntimeError("nvcc not found and no prebuilt libhf2d_gpu.so")
     cmd = [nvcc] + NVCC_FLAGS + os.environ.get("HF2D_NVCC_EXTRA", "").split() + ["-o", SO, os.path.join(CSRC, "hf2d_gpu.cu")]
     r = subprocess.run(cmd, capture_output=True, text=True)
@@ -40,6 +60,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
         print(log)
     if r.returncode != 0:
         raise RuntimeError("nvcc failed:\n" + log[-4000:])
+    with open(SO + ".srchash", "w") as f:
+        f.write(source_hash() + "\n")
     return SO
 
 
