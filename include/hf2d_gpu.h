@@ -304,6 +304,10 @@ int  hf2d_slab_download_local(hf2d_slab* s, void* J_slab, const hf2d_node_layout
  * The report is the undivided grid's (whole-grid residual norms; dt, time global). */
 int  hf2d_slab_run(hf2d_slab* const* local, int n_local, int nsteps, int new_cycle, hf2d_step_report* report);
 int  hf2d_slab_read_node(hf2d_slab* const* local, int n_local, int i_global, int j, double* p, double* Tg);
+/* hf2d_gpu_tecplot_format / _fetch for a grid cut into slabs, all driven by this process: every slab formats the lines of its owned
+ * columns on its own GPU, the host interleaves the row segments.  host_text == NULL: only *bytes is set; call again with a buffer. */
+int  hf2d_slab_tecplot(hf2d_slab* const* local, int n_local, const hf2d_node_layout* layout, int type, double dx_out, double dy_out,
+                       char* host_text, size_t* bytes);
 
 #ifdef __cplusplus
 }

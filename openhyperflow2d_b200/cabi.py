@@ -68,7 +68,7 @@ EXPORTS = ["hf2d_gpu_last_error", "hf2d_gpu_device_count", "hf2d_gpu_create", "h
            "hf2d_gpu_halo_unpack_lane", "hf2d_gpu_edge_tile_counts", "hf2d_gpu_set_min_distance_to_wall", "hf2d_gpu_set_global_time", "hf2d_gpu_recalc_y_plus", "hf2d_gpu_residual_sums", "hf2d_gpu_set_min_distance_to_wall_slab", "hf2d_gpu_keep_gradients",
            "hf2d_gpu_wall_distance_noalloc", "hf2d_slab_cuts", "hf2d_slab_create", "hf2d_slab_destroy", "hf2d_slab_solver", "hf2d_slab_columns",
            "hf2d_slab_ipc_handle_bytes", "hf2d_slab_ipc_handle", "hf2d_slab_connect_ipc", "hf2d_slab_connect_local", "hf2d_slab_upload",
-           "hf2d_slab_download", "hf2d_slab_upload_local", "hf2d_slab_download_local", "hf2d_slab_run", "hf2d_slab_read_node", "hf2d_gpu_tecplot_format", "hf2d_gpu_tecplot_fetch"]
+           "hf2d_slab_download", "hf2d_slab_upload_local", "hf2d_slab_download_local", "hf2d_slab_run", "hf2d_slab_read_node", "hf2d_gpu_tecplot_format", "hf2d_gpu_tecplot_fetch", "hf2d_slab_tecplot"]
 
 
 def lib():
@@ -127,6 +127,7 @@ def lib():
         L.hf2d_gpu_wall_distance_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.hf2d_gpu_tecplot_format.argtypes = [C.c_void_p, C.POINTER(NodeLayout), C.c_int, C.c_double, C.c_double, C.POINTER(C.c_size_t)]
         L.hf2d_gpu_tecplot_fetch.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
+        L.hf2d_slab_tecplot.argtypes = [C.c_void_p, C.c_int, C.POINTER(NodeLayout), C.c_int, C.c_double, C.c_double, C.c_void_p, C.POINTER(C.c_size_t)]
         L.hf2d_slab_cuts.argtypes = [C.c_void_p, C.POINTER(NodeLayout), C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
         L.hf2d_slab_create.argtypes = [C.POINTER(Cfg), C.c_int, C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]
         L.hf2d_slab_destroy.argtypes = [C.c_void_p]
@@ -471,3 +472,13 @@ class Slab:
 
     def run(self, nsteps: int, new_cycle: bool = True) -> StepReport:
         return Slab.run_all([self], nsteps, new_cycle)
+
+    @staticmethod
+    def tecplot_body(slabs, type_: int, dx_out: float, dy_out: float) -> bytes:
+        """hf2d_slab_tecplot: the body of SaveData2D for the whole grid, every slab formatted on its own GPU."""
+        arr = (C.c_void_p * len(slabs))(*[s._s for s in slabs])
+        n = C.c_size_t()
+        _ck(lib().hf2d_slab_tecplot(arr, len(slabs), C.byref(slabs[0].layout), int(type_), float(dx_out), float(dy_out), None, C.byref(n)))
+        buf = C.create_string_buffer(max(n.value, 1))
+        _ck(lib().hf2d_slab_tecplot(arr, len(slabs), C.byref(slabs[0].layout), int(type_), float(dx_out), float(dy_out), buf, C.byref(n)))
+        return buf.raw[:n.value]

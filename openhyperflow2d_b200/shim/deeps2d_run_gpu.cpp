@@ -77,16 +77,18 @@ static void eng_destroy() {
 // DataSnapshot (deeps2d_core.cpp:2494-2516) = CutFile if rewriting, OpenData (append mode), SaveData2D, close.  The two title
 // lines are written here exactly as SaveData2D writes them (:2594-2616); the 16-column body comes from
 // hf2d_gpu_tecplot_format / _fetch.  Falls back to the reference's own DataSnapshot where the formatter does not apply
-// (is_Cx_calc, is_p_asterisk_out, several slabs, no resident image).
+// (is_Cx_calc, is_p_asterisk_out, no resident image).
 extern int is_p_asterisk_out;
 static int g_gpu_tecplot = 0;
 static void snapshot(char* filename, WRITE_MODE mode, const hf2d_node_layout* lay) {
     size_t bytes = 0;
     const FP dx_out = (dx * MaxX) / (MaxX - 1), dy_out = (dy * MaxY) / (MaxY - 1);       // :2618-2619
-    if (!g_gpu_tecplot || g_nslab || is_Cx_calc || is_p_asterisk_out ||
-        hf2d_gpu_tecplot_format(g_h, lay, (int)mode, dx_out, dy_out, &bytes)) { DataSnapshot(filename, mode); return; }
+    if (!g_gpu_tecplot || is_Cx_calc || is_p_asterisk_out ||
+        (g_nslab ? hf2d_slab_tecplot(g_slab, g_nslab, lay, (int)mode, dx_out, dy_out, NULL, &bytes)
+                 : hf2d_gpu_tecplot_format(g_h, lay, (int)mode, dx_out, dy_out, &bytes))) { DataSnapshot(filename, mode); return; }
     char* text = (char*)malloc(bytes ? bytes : 1);
-    if (!text || hf2d_gpu_tecplot_fetch(g_h, text, bytes)) { free(text); DataSnapshot(filename, mode); return; }
+    if (!text || (g_nslab ? hf2d_slab_tecplot(g_slab, g_nslab, lay, (int)mode, dx_out, dy_out, text, &bytes)
+                          : hf2d_gpu_tecplot_fetch(g_h, text, bytes))) { free(text); DataSnapshot(filename, mode); return; }
     if (mode) CutFile(filename);
     ofstream* out = OpenData(filename);
     char t1[1024] = {0}, t2[256] = {0};

@@ -80,14 +80,18 @@ def test_device_tecplot_body_equals_the_host_writer(name, type_):
         raise AssertionError(f"{name}: {len(text)} vs {len(want)} bytes, first differing lines {bad}")
 
 
+@pytest.mark.parametrize("n_gpus", [1, 3])
 @pytest.mark.parametrize("case,nmax,nout,exit_time", [("euler_duct", 7, 3, 5e-7), ("ns_laminar", 6, 4, 4e-7)])
-def test_reference_program_writes_identical_plt_files_from_the_device(case, nmax, nout, exit_time, tmp_path):
+def test_reference_program_writes_identical_plt_files_from_the_device(case, nmax, nout, exit_time, n_gpus, tmp_path):
     import test_shim_dropin as D
     if not (os.path.exists(D.REF) and os.path.exists(D.GPU)):
         pytest.skip("oracle/_ref not built (make -C oracle ref)")
     deck = D._deck(case, nmax, nout, exit_time)
     D._run(D.REF, deck, case, str(tmp_path / "ref"))
-    _, _, out = D._run(D.GPU, deck, case, str(tmp_path / "gpu"), env={"HF2D_GPU_TECPLOT": "1"})
+    env = {"HF2D_GPU_TECPLOT": "1"}
+    if n_gpus > 1:          # three X-slabs (on as many GPUs as the box has): each formats its columns, the host interleaves the rows
+        env.update(HF2D_GPUS=str(n_gpus), CUDA_DEVICE_MAX_CONNECTIONS="32")
+    _, _, out = D._run(D.GPU, deck, case, str(tmp_path / "gpu"), env=env)
     assert "hf2d_gpu: Tecplot snapshots formatted on the GPU" in out
     for fn in (case + ".plt", "tp-" + case + ".plt"):
         a = open(tmp_path / "ref" / fn, "rb").read()
@@ -97,3 +101,32 @@ def test_reference_program_writes_identical_plt_files_from_the_device(case, nmax
             la, lb = a.split(b"\n"), b.split(b"\n")
             bad = [(q, x, y) for q, (x, y) in enumerate(zip(la, lb)) if x != y][:3]
             raise AssertionError(f"{fn}: {len(a)} vs {len(b)} bytes, first differing lines {bad}")
+
+
+@pytest.mark.parametrize("name,world,type_", [("ns_keps_std_n8", 3, 1), ("geometry/cylinders_keps_n8", 4, 0)])
+def test_slab_tecplot_body_equals_the_undivided_one(name, world, type_):
+    """hf2d_slab_tecplot: every slab formats its owned columns, the host interleaves the row segments -- the same bytes as the
+    single-GPU formatter on the undivided grid (the slabs reproduce its fields bit for bit)."""
+    import torch
+    from openhyperflow2d_b200 import cabi
+    c = load_case(name)
+    cfg = c["cfg"]
+    J = np.array(c["state0"], copy=True)
+    nx, ny = J.shape
+    dxo, dyo = (cfg["dx"] * nx) / (nx - 1), (cfg["dy"] * ny) / (ny - 1)
+    s = cabi.Solver(cfg, LAYOUT)
+    s.upload_aos(J)
+    s.step(c["nsteps"])
+    want = s.tecplot_body(type_, dxo, dyo)
+    s.close()
+    cuts = cabi.slab_cuts(J, LAYOUT, world)
+    nd = torch.cuda.device_count()
+    slabs = [cabi.Slab(cfg, LAYOUT, r % nd, r, world, cuts) for r in range(world)]
+    cabi.Slab.connect_local(slabs)
+    for sl in slabs:
+        sl.upload(J)
+    cabi.Slab.run_all(slabs, c["nsteps"])
+    got = cabi.Slab.tecplot_body(slabs, type_, dxo, dyo)
+    for sl in slabs:
+        sl.close()
+    assert len(got) == len(want) and got == want
