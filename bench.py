@@ -435,6 +435,25 @@ def main():
         ss.close()
         line["same_grid_as_reference_arm"] = {"grid": f"{REF_NX}x{REF_NY}", "active_cells": a_s, "steps": 200, "ms_per_step": rs.gpu_ms / 200,
                                               "value": a_s * 200 / (rs.gpu_ms * 1e-3), "unit": UNIT}
+    if world == 1 and not args.no_e2e:
+        # the output step behind the hot loop: the body of the reference's Tecplot snapshot (SaveData2D, 16 "%g"
+        # columns per node) formatted on the device from the state the timed steps left, and copied to the host
+        try:
+            import ctypes as C
+            n = C.c_size_t()
+            dxo, dyo = runner.cfg["dx"] * args.nx / (args.nx - 1), runner.cfg["dy"] * args.ny / (args.ny - 1)
+            t0 = time.perf_counter()
+            cabi._ck(cabi.lib().hf2d_gpu_tecplot_format(runner.solver._h, C.byref(runner.solver.layout), 0, dxo, dyo, C.byref(n)))
+            t1 = time.perf_counter()
+            buf = C.create_string_buffer(max(n.value, 1))
+            t2 = time.perf_counter()
+            cabi._ck(cabi.lib().hf2d_gpu_tecplot_fetch(runner.solver._h, buf, n.value))
+            t3 = time.perf_counter()
+            line["tecplot_snapshot"] = {"lines": args.nx * args.ny, "text_bytes": n.value, "format_ms": (t1 - t0) * 1e3, "fetch_ms": (t3 - t2) * 1e3,
+                                        "note": "hf2d_gpu_tecplot_format + _fetch, FIRST call (includes allocating the line slots and loading the kernels; 33 ms repeated, profiles/r2_tecplot.json); byte-identical with the reference SaveData2D body (tests/test_zz_tecplot_gpu.py)"}
+            del buf
+        except Exception as e:      # never fails the bench line
+            line["tecplot_snapshot"] = {"error": str(e)[:200]}
     if parity is not None:
         line["parity"] = parity
     if not args.no_e2e:
